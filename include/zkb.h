@@ -1,0 +1,186 @@
+/*
+ * zkb.h -- C ABI of the B200-native Groth16 prover backend for zklaim (libzkb.so).
+ *
+ * Drop-in boundary: everything above this header is the unchanged
+ * reference host code -- zklaim's C API (zklaim/zklaim.h:117-262), the C++ bridge
+ * (zklaim/libsnark_wrapper.cpp:195-276), gadget witness generation
+ * (zklaim/zklaim_gadget.cpp:705-783) and libsnark's key/proof (de)serialisation.  The single
+ * call that moves to the GPU is
+ *
+ *     zklaim/snark.cpp:126
+ *         return r1cs_gg_ppzksnark_prover<ppT>(proving_key, pb.primary_input(), pb.auxiliary_input());
+ *     (signature: libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.hpp:373-376)
+ *
+ * which becomes zkb_key_upload() (once per proving key) + zkb_prove() (per proof); see
+ * INTEGRATION.md for the bridge-side stub.  The other entry points expose the sub-steps
+ * of that call for the reference's own micro-benchmarks (multi_exp, evaluation-domain
+ * FFTs, r1cs_to_qap_witness_map) and for parity tests of the arithmetic layers.
+ *
+ * Conventions
+ *   - plain C, no C++ types, no exceptions cross this boundary; nothing aborts.
+ *   - return value: 0 = ok, < 0 = error (zkb_last_error() gives the text).
+ *   - all host buffers are caller-owned; the library copies what it keeps.
+ *   - one zkb_ctx per host thread (it owns one CUDA stream and its scratch memory);
+ *     zkb_key / zkb_bases are immutable after creation and may be shared by contexts on
+ *     the same device.
+ *   - field elements: 4 x uint64_t little-endian limbs, Montgomery form (R = 2^256),
+ *     canonical (< modulus) -- bit-identical to libff's Fp_model::mont_repr
+ *     (libff/algebra/fields/fp.hpp:42).  Fq2 = c0 then c1.
+ *   - G1 affine: x, y (8 limbs); G2 affine: x.c0 x.c1 y.c0 y.c1 (16 limbs); the point at
+ *     infinity is all-zero limbs.  This is the in-memory form of a key after libsnark's
+ *     operator>> (alt_bn128_g1.cpp:453-462: Z = 1 or zero).
+ *   - G1 Jacobian: X, Y, Z (12 limbs) as alt_bn128_g1.hpp:35; G2 Jacobian 24 limbs.
+ *     Infinity <=> Z == 0.  Outputs are some representative of the group element (the
+ *     reference normalises to affine when it serialises, alt_bn128_g1.cpp:404-418).
+ */
+#ifndef ZKB_H
+#define ZKB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct zkb_ctx zkb_ctx;
+typedef struct zkb_bases zkb_bases;
+typedef struct zkb_key zkb_key;
+
+enum {
+    ZKB_OK = 0,
+    ZKB_ERR_CUDA = -1,     /* a CUDA call failed (no device, out of memory, launch error) */
+    ZKB_ERR_ARG = -2,      /* bad argument */
+    ZKB_ERR_DOMAIN = -3,   /* no supported evaluation domain for this size */
+    ZKB_ERR_UNSAT = -4     /* witness does not satisfy the constraint system */
+};
+
+/* field / group selectors for the element-wise entry points */
+enum { ZKB_FR = 0, ZKB_FQ = 1, ZKB_FQ2 = 2 };
+enum { ZKB_OP_ADD = 0, ZKB_OP_SUB = 1, ZKB_OP_MUL = 2, ZKB_OP_SQR = 3, ZKB_OP_INV = 4, ZKB_OP_NEG = 5 };
+enum { ZKB_G1 = 1, ZKB_G2 = 2 };
+/* group ops on Jacobian operands: a + b, 2a, a + b with b affine-normalised (Z = 1), -a */
+enum { ZKB_GOP_ADD = 0, ZKB_GOP_DBL = 1, ZKB_GOP_MIXED_ADD = 2, ZKB_GOP_NEG = 3 };
+/* evaluation-domain kinds, numbered as libfqfft's factory tries them
+ * (libfqfft/evaluation_domain/get_evaluation_domain.tcc:33-52) */
+enum { ZKB_DOMAIN_BASIC_RADIX2 = 1, ZKB_DOMAIN_EXTENDED_RADIX2 = 2, ZKB_DOMAIN_STEP_RADIX2 = 3 };
+/* domain operations = evaluation_domain<Fr> members (libfqfft/evaluation_domain/evaluation_domain.hpp:36-99),
+ * coset shift fixed to Fr::multiplicative_generator as in r1cs_to_qap.tcc:262-311 */
+enum { ZKB_NTT_FFT = 0, ZKB_NTT_IFFT = 1, ZKB_NTT_COSET_FFT = 2, ZKB_NTT_ICOSET_FFT = 3, ZKB_NTT_DIV_Z_ON_COSET = 4 };
+
+/* ---- lifetime ---------------------------------------------------------------------- */
+/* Creates a context on CUDA device `device_id`.  Fails (ZKB_ERR_CUDA) when no GPU is
+ * present: there is no CPU fallback anywhere in this library. */
+int zkb_init(int device_id, zkb_ctx **out);
+void zkb_shutdown(zkb_ctx *ctx);
+const char *zkb_last_error(const zkb_ctx *ctx); /* ctx may be NULL: last error of zkb_init */
+const char *zkb_version(void);
+
+/* ---- K1-K3: element-wise arithmetic (parity tests of the field / group layers) ------- */
+/* libff Fp_model / Fp2_model operators (fp.tcc, fp2.tcc); b may be NULL for unary ops;
+ * n elements of 4 limbs (8 for ZKB_FQ2). */
+int zkb_field_op(zkb_ctx *ctx, int field, int op, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t n);
+/* alt_bn128_G1 / alt_bn128_G2 operator+, dbl, mixed_add, unary minus
+ * (alt_bn128_g1.cpp:139-358, alt_bn128_g2.cpp:149-365) on Jacobian limbs. */
+int zkb_group_op(zkb_ctx *ctx, int group, int op, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t n);
+/* scalar * point, libff operator*(Fr, G) (curve_utils.tcc:13-34): scalars Montgomery Fr, points Jacobian. */
+int zkb_group_scalar_mul(zkb_ctx *ctx, int group, const uint64_t *scalars, const uint64_t *points, uint64_t *out,
+                         size_t n);
+
+/* ---- K4/K5: multi-scalar multiplication ------------------------------------------- */
+/* Uploads n affine bases and (precompute_factor > 1) their 2^(j*G*c) multiples so that up
+ * to `precompute_factor` windows share one bucket set (HBM for doublings; B200 has 180 GB).
+ * window_bits = 0 lets the library choose c from n.  precompute_factor = 0 means "all
+ * windows" (no doublings at all at MSM time), 1 means none. */
+int zkb_bases_upload(zkb_ctx *ctx, int group, const uint64_t *affine, size_t n, int window_bits,
+                     int precompute_factor, zkb_bases **out);
+void zkb_bases_free(zkb_bases *b);
+size_t zkb_bases_device_bytes(const zkb_bases *b);
+
+/* sum_i scalars[i] * bases[offset + i], i < n -- libff::multi_exp<T, Fr, multi_exp_method_BDLO12>
+ * and multi_exp_with_mixed_addition (multiexp.tcc:402-496).  scalars: host, Montgomery Fr.
+ * out: Jacobian limbs (12 for G1, 24 for G2). */
+int zkb_msm(zkb_ctx *ctx, const zkb_bases *bases, size_t offset, const uint64_t *scalars, size_t n, uint64_t *out);
+/* Same with the scalars already in device memory (d_scalars is a CUDA device pointer);
+ * the result stays on the host (it is 96 / 192 bytes). */
+int zkb_msm_device(zkb_ctx *ctx, const zkb_bases *bases, size_t offset, const void *d_scalars, size_t n,
+                   uint64_t *out);
+
+/* ---- K7-K9: evaluation domains ---------------------------------------------------- */
+/* libfqfft::get_evaluation_domain<Fr>(min_size) (get_evaluation_domain.tcc:33-52): the
+ * domain size m and kind the reference would pick.  Host-only, needs no ctx. */
+int zkb_domain_select(size_t min_size, size_t *m_out, int *kind_out);
+/* In-place domain operation on m = domain size elements of host memory. */
+int zkb_domain_op(zkb_ctx *ctx, size_t min_size, int op, uint64_t *data);
+
+/* ---- the proving key ---------------------------------------------------------------- */
+/* CSR of one R1CS matrix: row i = constraint i; col 0 = the constant 1, col j > 0 = variable
+ * j-1 of the full assignment (libsnark/relations/variable.tcc:262-270). */
+typedef struct {
+    const uint64_t *row_ptr; /* num_constraints + 1 */
+    const uint32_t *col;     /* nnz */
+    const uint64_t *coeff;   /* nnz x 4 limbs, Montgomery Fr */
+} zkb_csr;
+
+/* r1cs_gg_ppzksnark_proving_key (r1cs_gg_ppzksnark.hpp:69-150) as flat arrays. */
+typedef struct {
+    size_t num_constraints, num_variables, num_inputs;
+    zkb_csr A, B, C;          /* pk.constraint_system (already A/B-swapped by the generator) */
+    const uint64_t *alpha_g1; /* 8 limbs affine */
+    const uint64_t *beta_g1;
+    const uint64_t *delta_g1;
+    const uint64_t *beta_g2;  /* 16 limbs affine */
+    const uint64_t *delta_g2;
+    const uint64_t *A_query;  /* (num_variables + 1) x 8 */
+    size_t B_nnz;
+    const uint32_t *B_index;  /* sparse_vector indices, ascending (sparse_vector.tcc:141-147) */
+    const uint64_t *B_g1;     /* B_nnz x 8   (knowledge_commitment::h) */
+    const uint64_t *B_g2;     /* B_nnz x 16  (knowledge_commitment::g) */
+    size_t H_size;            /* domain m - 1 */
+    const uint64_t *H_query;  /* H_size x 8 */
+    const uint64_t *L_query;  /* (num_variables - num_inputs) x 8 */
+} zkb_key_desc;
+
+int zkb_key_upload(zkb_ctx *ctx, const zkb_key_desc *desc, zkb_key **out);
+void zkb_key_free(zkb_key *key);
+size_t zkb_key_device_bytes(const zkb_key *key);
+/* domain chosen for this key (what r1cs_to_qap_witness_map would use, r1cs_to_qap.tcc:218) */
+int zkb_key_domain(const zkb_key *key, size_t *m_out, int *kind_out);
+
+/* ---- K10 + K7/K8: r1cs_to_qap_witness_map (r1cs_to_qap.tcc:205-334, d1 = d2 = d3 = 0) ---- */
+/* w: num_variables x 4 limbs (primary then auxiliary).  H_out: (m + 1) x 4 limbs. */
+int zkb_witness_map(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, uint64_t *H_out);
+
+/* ---- the prover --------------------------------------------------------------------- */
+typedef struct {
+    uint64_t A[12]; /* g_A, G1 Jacobian */
+    uint64_t B[24]; /* g_B, G2 Jacobian */
+    uint64_t C[12]; /* g_C, G1 Jacobian */
+} zkb_proof;
+
+/* r1cs_gg_ppzksnark_prover (r1cs_gg_ppzksnark.tcc:390-505) with the blinding scalars r, s
+ * (:418-419) supplied by the caller (Montgomery Fr).  H_out (optional, may be NULL)
+ * receives coefficients_for_H, (m + 1) x 4 limbs.  Returns ZKB_ERR_UNSAT if the H
+ * polynomial's top coefficients are non-zero, i.e. the witness does not satisfy the
+ * system (the reference asserts this, :406-408). */
+int zkb_prove(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4],
+              zkb_proof *out, uint64_t *H_out);
+
+/* `count` independent proofs under one key; w, r, s, out are arrays of `count` items
+ * (w: count x num_variables x 4).  The batch is pipelined on the context's device. */
+int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r,
+                    const uint64_t *s, zkb_proof *out);
+
+/* ---- measurement helpers (used by bench.py only) ------------------------------------ */
+/* Sustained integer multiply-add rate of the device: independent mad.wide.u32 chains on all
+ * SMs; returns 32x32+64->64 multiply-adds per second, or < 0 on error. */
+double zkb_measure_imad_peak(zkb_ctx *ctx, int iters);
+/* Device milliseconds (CUDA events on the context's stream) of the kernels launched by the most
+ * recent zkb_msm* / zkb_witness_map / zkb_prove* call, and how many kernels that was. */
+double zkb_last_device_ms(const zkb_ctx *ctx);
+long zkb_last_kernel_launches(const zkb_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZKB_H */

@@ -1,0 +1,317 @@
+"""zklaim_b200 -- host-side (Python) mirror of the zkb C ABI (include/zkb.h).
+
+The product is ``libzkb.so`` (hand-written sm_100a CUDA behind a plain C ABI, see
+``include/zkb.h``); this module is the thin ctypes layer used by the tests and by
+``bench.py``.  There is no CPU fallback: importing works without a GPU (so that the
+symbol table can be checked), but creating a :class:`Context` raises when no CUDA device
+is present or when the library has not been built.
+
+Array conventions (numpy, dtype uint64, C-contiguous), identical to libff's memory layout:
+  Fr / Fq      (..., 4)   Montgomery limbs     (libff/algebra/fields/fp.hpp:42)
+  Fq2          (..., 8)
+  G1 affine    (..., 8)   x, y; all-zero = infinity
+  G2 affine    (..., 16)
+  G1 Jacobian  (..., 12)  X, Y, Z              (alt_bn128_g1.hpp:35)
+  G2 Jacobian  (..., 24)
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libzkb.so")
+
+FR, FQ, FQ2 = 0, 1, 2
+G1, G2 = 1, 2
+OP_ADD, OP_SUB, OP_MUL, OP_SQR, OP_INV, OP_NEG = range(6)
+GOP_ADD, GOP_DBL, GOP_MIXED_ADD, GOP_NEG = range(4)
+NTT_FFT, NTT_IFFT, NTT_COSET_FFT, NTT_ICOSET_FFT, NTT_DIV_Z_ON_COSET = range(5)
+DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2 = 1, 2, 3
+ERR_UNSAT = -4
+
+# every symbol include/zkb.h declares: (name, restype, argtypes)
+_vp, _sz, _i, _u64p = C.c_void_p, C.c_size_t, C.c_int, C.c_void_p
+SYMBOLS = {
+    "zkb_init": (_i, [_i, C.POINTER(_vp)]),
+    "zkb_shutdown": (None, [_vp]),
+    "zkb_last_error": (C.c_char_p, [_vp]),
+    "zkb_version": (C.c_char_p, []),
+    "zkb_field_op": (_i, [_vp, _i, _i, _u64p, _u64p, _u64p, _sz]),
+    "zkb_group_op": (_i, [_vp, _i, _i, _u64p, _u64p, _u64p, _sz]),
+    "zkb_group_scalar_mul": (_i, [_vp, _i, _u64p, _u64p, _u64p, _sz]),
+    "zkb_bases_upload": (_i, [_vp, _i, _u64p, _sz, _i, _i, C.POINTER(_vp)]),
+    "zkb_bases_free": (None, [_vp]),
+    "zkb_bases_device_bytes": (_sz, [_vp]),
+    "zkb_msm": (_i, [_vp, _vp, _sz, _u64p, _sz, _u64p]),
+    "zkb_msm_device": (_i, [_vp, _vp, _sz, _vp, _sz, _u64p]),
+    "zkb_domain_select": (_i, [_sz, C.POINTER(_sz), C.POINTER(_i)]),
+    "zkb_domain_op": (_i, [_vp, _sz, _i, _u64p]),
+    "zkb_key_upload": (_i, [_vp, _vp, C.POINTER(_vp)]),
+    "zkb_key_free": (None, [_vp]),
+    "zkb_key_device_bytes": (_sz, [_vp]),
+    "zkb_key_domain": (_i, [_vp, C.POINTER(_sz), C.POINTER(_i)]),
+    "zkb_witness_map": (_i, [_vp, _vp, _u64p, _u64p]),
+    "zkb_prove": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _vp, _u64p]),
+    "zkb_prove_batch": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p, _vp]),
+    "zkb_measure_imad_peak": (C.c_double, [_vp, _i]),
+    "zkb_last_device_ms": (C.c_double, [_vp]),
+    "zkb_last_kernel_launches": (C.c_long, [_vp]),
+}
+
+
+class ZkbError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"zkb error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen libzkb.so and bind every symbol of include/zkb.h.  Raises if it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise ZkbError(-1, f"{p} not built (run zklaim_b200/build.sh or __graft_entry__.build()); "
+                           "there is no CPU fallback")
+    lib = C.CDLL(p)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def _arr(a, last: int) -> np.ndarray:
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    if a.shape[-1] != last:
+        raise ValueError(f"expected last dimension {last}, got {a.shape}")
+    return a
+
+
+class _CSR(C.Structure):
+    _fields_ = [("row_ptr", C.c_void_p), ("col", C.c_void_p), ("coeff", C.c_void_p)]
+
+
+class _KeyDesc(C.Structure):
+    _fields_ = [
+        ("num_constraints", C.c_size_t), ("num_variables", C.c_size_t), ("num_inputs", C.c_size_t),
+        ("A", _CSR), ("B", _CSR), ("C", _CSR),
+        ("alpha_g1", C.c_void_p), ("beta_g1", C.c_void_p), ("delta_g1", C.c_void_p),
+        ("beta_g2", C.c_void_p), ("delta_g2", C.c_void_p),
+        ("A_query", C.c_void_p), ("B_nnz", C.c_size_t), ("B_index", C.c_void_p),
+        ("B_g1", C.c_void_p), ("B_g2", C.c_void_p),
+        ("H_size", C.c_size_t), ("H_query", C.c_void_p), ("L_query", C.c_void_p),
+    ]
+
+
+class Proof(C.Structure):
+    _fields_ = [("A", C.c_uint64 * 12), ("B", C.c_uint64 * 24), ("C", C.c_uint64 * 12)]
+
+    def as_array(self) -> np.ndarray:
+        return np.concatenate([np.array(self.A, dtype=np.uint64), np.array(self.B, dtype=np.uint64),
+                               np.array(self.C, dtype=np.uint64)])
+
+
+class Context:
+    """One zkb_ctx: a CUDA stream plus scratch memory on one device."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.zkb_init(device, C.byref(h))
+        if rc:
+            raise ZkbError(rc, self.lib.zkb_last_error(None).decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.zkb_shutdown(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc: int):
+        if rc:
+            raise ZkbError(rc, self.lib.zkb_last_error(self.h).decode())
+
+    # ---- element-wise -----------------------------------------------------------------
+    def field_op(self, field: int, op: int, a, b=None) -> np.ndarray:
+        w = 8 if field == FQ2 else 4
+        a = _arr(a, w)
+        out = np.empty_like(a)
+        bp = None
+        if b is not None:
+            b = _arr(b, w)
+            assert b.shape == a.shape
+            bp = b.ctypes.data
+        self._chk(self.lib.zkb_field_op(self.h, field, op, a.ctypes.data, bp, out.ctypes.data, a.size // w))
+        return out
+
+    def group_op(self, group: int, op: int, a, b=None) -> np.ndarray:
+        w = 12 if group == G1 else 24
+        a = _arr(a, w)
+        out = np.empty_like(a)
+        bp = None
+        if b is not None:
+            b = _arr(b, w)
+            assert b.shape == a.shape
+            bp = b.ctypes.data
+        self._chk(self.lib.zkb_group_op(self.h, group, op, a.ctypes.data, bp, out.ctypes.data, a.size // w))
+        return out
+
+    def scalar_mul(self, group: int, scalars, points) -> np.ndarray:
+        w = 12 if group == G1 else 24
+        s = _arr(scalars, 4)
+        p = _arr(points, w)
+        out = np.empty_like(p)
+        self._chk(self.lib.zkb_group_scalar_mul(self.h, group, s.ctypes.data, p.ctypes.data, out.ctypes.data,
+                                                p.size // w))
+        return out
+
+    # ---- MSM --------------------------------------------------------------------------
+    def upload_bases(self, group: int, affine, window_bits: int = 0, precompute_factor: int = 0) -> "Bases":
+        w = 8 if group == G1 else 16
+        a = _arr(affine, w)
+        h = C.c_void_p()
+        self._chk(self.lib.zkb_bases_upload(self.h, group, a.ctypes.data, a.size // w, window_bits,
+                                            precompute_factor, C.byref(h)))
+        return Bases(self, h, group, a.size // w)
+
+    def msm(self, bases: "Bases", scalars, offset: int = 0) -> np.ndarray:
+        s = _arr(scalars, 4)
+        out = np.zeros(12 if bases.group == G1 else 24, dtype=np.uint64)
+        self._chk(self.lib.zkb_msm(self.h, bases.h, offset, s.ctypes.data, s.size // 4, out.ctypes.data))
+        return out
+
+    def msm_device(self, bases: "Bases", d_scalars_ptr: int, n: int, offset: int = 0) -> np.ndarray:
+        out = np.zeros(12 if bases.group == G1 else 24, dtype=np.uint64)
+        self._chk(self.lib.zkb_msm_device(self.h, bases.h, offset, d_scalars_ptr, n, out.ctypes.data))
+        return out
+
+    # ---- domains ----------------------------------------------------------------------
+    def domain_op(self, min_size: int, op: int, data) -> np.ndarray:
+        d = np.array(_arr(data, 4), copy=True)
+        self._chk(self.lib.zkb_domain_op(self.h, min_size, op, d.ctypes.data))
+        return d
+
+    # ---- key / prover -----------------------------------------------------------------
+    def upload_key(self, key: dict) -> "Key":
+        """key: dict with the fields of zkb_key_desc as numpy arrays (see oracle.zkref.export_key)."""
+        keep = []
+
+        def ptr(a, dtype=np.uint64):
+            a = np.ascontiguousarray(a, dtype=dtype)
+            keep.append(a)
+            return a.ctypes.data
+
+        d = _KeyDesc()
+        d.num_constraints, d.num_variables, d.num_inputs = key["num_constraints"], key["num_variables"], key["num_inputs"]
+        for name in "ABC":
+            rp, col, co = key["csr_" + name]
+            setattr(d, name, _CSR(ptr(rp), ptr(col, np.uint32), ptr(co)))
+        for f in ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "delta_g2", "A_query", "B_g1", "B_g2", "H_query",
+                  "L_query"):
+            setattr(d, f, ptr(key[f]))
+        d.B_index = ptr(key["B_index"], np.uint32)
+        d.B_nnz = len(key["B_index"])
+        d.H_size = len(key["H_query"])
+        h = C.c_void_p()
+        self._chk(self.lib.zkb_key_upload(self.h, C.byref(d), C.byref(h)))
+        return Key(self, h, key["num_variables"])
+
+    def witness_map(self, key: "Key", w) -> np.ndarray:
+        w = _arr(w, 4)
+        m, _ = key.domain()
+        H = np.zeros((m + 1, 4), dtype=np.uint64)
+        self._chk(self.lib.zkb_witness_map(self.h, key.h, w.ctypes.data, H.ctypes.data))
+        return H
+
+    def prove(self, key: "Key", w, r, s, want_H: bool = False):
+        w = _arr(w, 4)
+        r = _arr(r, 4)
+        s = _arr(s, 4)
+        pr = Proof()
+        H = None
+        hp = None
+        if want_H:
+            m, _ = key.domain()
+            H = np.zeros((m + 1, 4), dtype=np.uint64)
+            hp = H.ctypes.data
+        self._chk(self.lib.zkb_prove(self.h, key.h, w.ctypes.data, r.ctypes.data, s.ctypes.data, C.byref(pr), hp))
+        return (pr.as_array(), H) if want_H else pr.as_array()
+
+    def prove_batch(self, key: "Key", w, r, s) -> np.ndarray:
+        w = _arr(w, 4)
+        r = _arr(r, 4)
+        s = _arr(s, 4)
+        count = r.shape[0]
+        assert w.shape[0] == count and s.shape[0] == count
+        out = (Proof * count)()
+        self._chk(self.lib.zkb_prove_batch(self.h, key.h, count, w.ctypes.data, r.ctypes.data, s.ctypes.data, out))
+        return np.stack([p.as_array() for p in out])
+
+    # ---- measurement ------------------------------------------------------------------
+    def imad_peak(self, iters: int = 4096) -> float:
+        return float(self.lib.zkb_measure_imad_peak(self.h, iters))
+
+    def last_device_ms(self) -> float:
+        return float(self.lib.zkb_last_device_ms(self.h))
+
+    def kernel_launches(self) -> int:
+        return int(self.lib.zkb_last_kernel_launches(self.h))
+
+
+class Bases:
+    def __init__(self, ctx: Context, h, group: int, n: int):
+        self.ctx, self.h, self.group, self.n = ctx, h, group, n
+
+    def device_bytes(self) -> int:
+        return int(self.ctx.lib.zkb_bases_device_bytes(self.h))
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.zkb_bases_free(self.h)
+            self.h = None
+
+
+class Key:
+    def __init__(self, ctx: Context, h, nv: int):
+        self.ctx, self.h, self.num_variables = ctx, h, nv
+
+    def domain(self):
+        m, k = C.c_size_t(), C.c_int()
+        self.ctx._chk(self.ctx.lib.zkb_key_domain(self.h, C.byref(m), C.byref(k)))
+        return int(m.value), int(k.value)
+
+    def device_bytes(self) -> int:
+        return int(self.ctx.lib.zkb_key_device_bytes(self.h))
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.zkb_key_free(self.h)
+            self.h = None
+
+
+def domain_select(min_size: int):
+    """libfqfft::get_evaluation_domain's choice (m, kind) for min_size; host only."""
+    lib = load_library()
+    m, k = C.c_size_t(), C.c_int()
+    rc = lib.zkb_domain_select(min_size, C.byref(m), C.byref(k))
+    if rc:
+        raise ZkbError(rc, "no supported evaluation domain")
+    return int(m.value), int(k.value)

@@ -1,0 +1,122 @@
+// common.cuh -- context, error handling, scratch memory and vectorised point I/O shared by
+// the translation units of libzkb.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/zkb.h"
+#include "ec.cuh"
+
+namespace zkb {
+
+// grow-only device buffer (scratch memory owned by a context)
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T *as() const { return (T *)p; }
+};
+
+} // namespace zkb
+
+struct zkb_ctx {
+    int dev = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    double last_ms = 0.0;
+    long launches = 0;
+    // scratch (grow-only); indices are private to each translation unit
+    zkb::DevBuf scratch[24];
+    void *pinned = nullptr; // small pinned staging area for results
+    size_t pinned_cap = 0;
+};
+
+namespace zkb {
+
+extern thread_local std::string g_init_err;
+
+inline int fail(zkb_ctx *ctx, int code, const std::string &msg)
+{
+    if (ctx)
+        ctx->err = msg;
+    else
+        g_init_err = msg;
+    return code;
+}
+
+#define ZKB_CUDA(ctx, call)                                                                                          \
+    do {                                                                                                             \
+        cudaError_t e__ = (call);                                                                                    \
+        if (e__ != cudaSuccess)                                                                                      \
+            return zkb::fail(ctx, ZKB_ERR_CUDA,                                                                      \
+                             std::string(#call) + ": " + cudaGetErrorString(e__) + " (" + __FILE__ + ":" +           \
+                                 std::to_string(__LINE__) + ")");                                                    \
+    } while (0)
+
+#define ZKB_LAUNCH_CHECK(ctx)                                                                                        \
+    do {                                                                                                             \
+        (ctx)->launches++;                                                                                           \
+        cudaError_t e__ = cudaGetLastError();                                                                        \
+        if (e__ != cudaSuccess)                                                                                      \
+            return zkb::fail(ctx, ZKB_ERR_CUDA,                                                                      \
+                             std::string("kernel launch: ") + cudaGetErrorString(e__) + " (" + __FILE__ + ":" +      \
+                                 std::to_string(__LINE__) + ")");                                                    \
+    } while (0)
+
+// ---- vectorised 16-byte global access for field elements / points -----------------------
+template <class T> __device__ __forceinline__ T ld_vec(const T *p)
+{
+    static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
+    T r;
+    const uint4 *s = reinterpret_cast<const uint4 *>(p);
+    uint4 *d = reinterpret_cast<uint4 *>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); i++) d[i] = s[i];
+    return r;
+}
+template <class T> __device__ __forceinline__ T ld_vec_ro(const T *p)
+{
+    static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
+    T r;
+    const uint4 *s = reinterpret_cast<const uint4 *>(p);
+    uint4 *d = reinterpret_cast<uint4 *>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); i++) d[i] = __ldg(s + i);
+    return r;
+}
+template <class T> __device__ __forceinline__ void st_vec(T *p, const T &v)
+{
+    static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
+    uint4 *d = reinterpret_cast<uint4 *>(p);
+    const uint4 *s = reinterpret_cast<const uint4 *>(&v);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); i++) d[i] = s[i];
+}
+
+inline unsigned ceil_div(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+// host-side helpers implemented in api.cu
+int ensure_pinned(zkb_ctx *ctx, size_t bytes);
+
+} // namespace zkb
