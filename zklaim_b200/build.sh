@@ -18,5 +18,5 @@ for src in *.cu; do
   fi
 done
 for p in "${pids[@]}"; do wait $p; done
-$NVCC -shared -o $OUT $OBJ/*.o -gencode arch=compute_100a,code=sm_100a -lcudart
+$NVCC -shared -o $OUT $OBJ/*.o -gencode arch=compute_100a,code=sm_100a
 echo "built $(realpath $OUT)"
