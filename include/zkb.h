@@ -59,8 +59,9 @@ enum {
 enum { ZKB_FR = 0, ZKB_FQ = 1, ZKB_FQ2 = 2 };
 enum { ZKB_OP_ADD = 0, ZKB_OP_SUB = 1, ZKB_OP_MUL = 2, ZKB_OP_SQR = 3, ZKB_OP_INV = 4, ZKB_OP_NEG = 5 };
 enum { ZKB_G1 = 1, ZKB_G2 = 2 };
-/* group ops on Jacobian operands: a + b, 2a, a + b with b affine-normalised (Z = 1), -a */
-enum { ZKB_GOP_ADD = 0, ZKB_GOP_DBL = 1, ZKB_GOP_MIXED_ADD = 2, ZKB_GOP_NEG = 3 };
+/* group ops on Jacobian operands: a + b, 2a, a + b with b affine-normalised (Z = 1), -a,
+ * to_affine_coordinates (alt_bn128_g1.cpp:60-77: Z = 1, or the zero (0, 1, 0)) */
+enum { ZKB_GOP_ADD = 0, ZKB_GOP_DBL = 1, ZKB_GOP_MIXED_ADD = 2, ZKB_GOP_NEG = 3, ZKB_GOP_NORMALIZE = 4 };
 /* evaluation-domain kinds, numbered as libfqfft's factory tries them
  * (libfqfft/evaluation_domain/get_evaluation_domain.tcc:33-52) */
 enum { ZKB_DOMAIN_BASIC_RADIX2 = 1, ZKB_DOMAIN_EXTENDED_RADIX2 = 2, ZKB_DOMAIN_STEP_RADIX2 = 3 };

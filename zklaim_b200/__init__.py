@@ -28,7 +28,7 @@ LIB_PATH = os.path.join(_HERE, "libzkb.so")
 FR, FQ, FQ2 = 0, 1, 2
 G1, G2 = 1, 2
 OP_ADD, OP_SUB, OP_MUL, OP_SQR, OP_INV, OP_NEG = range(6)
-GOP_ADD, GOP_DBL, GOP_MIXED_ADD, GOP_NEG = range(4)
+GOP_ADD, GOP_DBL, GOP_MIXED_ADD, GOP_NEG, GOP_NORMALIZE = range(5)
 NTT_FFT, NTT_IFFT, NTT_COSET_FFT, NTT_ICOSET_FFT, NTT_DIV_Z_ON_COSET = range(5)
 DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2 = 1, 2, 3
 ERR_UNSAT = -4

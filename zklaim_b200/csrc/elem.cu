@@ -50,6 +50,22 @@ template <class F> __global__ void k_group_op(int op, const Jacobian<F> *a, cons
         x.madd(p);
         break;
     }
+    case ZKB_GOP_NORMALIZE: {
+        // the reference's to_affine_coordinates (alt_bn128_g1.cpp:60-77): (X/Z^2, Y/Z^3, 1) or zero (0, 1, 0)
+        Jacobian<F> j;
+        if (x.is_inf()) {
+            j.X = F::zero();
+            j.Y = F::one();
+            j.Z = F::zero();
+        } else {
+            const F inv = (x.ZZ * x.ZZZ).inverse();
+            j.X = x.X * (inv * x.ZZZ);
+            j.Y = x.Y * (inv * x.ZZ);
+            j.Z = F::one();
+        }
+        st_vec(o + i, j);
+        return;
+    }
     default: x = x.neg(); break;
     }
     st_vec(o + i, x.to_jacobian());
@@ -107,7 +123,7 @@ int zkb_field_op(zkb_ctx *ctx, int field, int op, const uint64_t *a, const uint6
 
 int zkb_group_op(zkb_ctx *ctx, int group, int op, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t n)
 {
-    if (!ctx || !a || !out || (group != ZKB_G1 && group != ZKB_G2) || op < 0 || op > ZKB_GOP_NEG)
+    if (!ctx || !a || !out || (group != ZKB_G1 && group != ZKB_G2) || op < 0 || op > ZKB_GOP_NORMALIZE)
         return fail(ctx, ZKB_ERR_ARG, "zkb_group_op: bad argument");
     if ((op == ZKB_GOP_ADD || op == ZKB_GOP_MIXED_ADD) && !b)
         return fail(ctx, ZKB_ERR_ARG, "zkb_group_op: binary op needs b");
