@@ -97,12 +97,12 @@ double zkb_measure_imad_peak(zkb_ctx *ctx, int iters)
     if (!ctx) return -1.0;
     if (iters <= 0) iters = 4096;
     if (cudaSetDevice(ctx->dev) != cudaSuccess) return -1.0;
-    if (ctx->scratch[23].ensure(64) != cudaSuccess) return -1.0;
+    if (ctx->scratch[SB_MISC].ensure(64) != cudaSuccess) return -1.0;
     const int blocks = ctx->sm_count * 8, threads = 256;
     double best = 0;
     for (int rep = 0; rep < 4; rep++) {
         cudaEventRecord(ctx->ev0, ctx->stream);
-        k_imad_peak<<<blocks, threads, 0, ctx->stream>>>(ctx->scratch[23].as<uint64_t>(), iters, 12345u + rep);
+        k_imad_peak<<<blocks, threads, 0, ctx->stream>>>(ctx->scratch[SB_MISC].as<uint64_t>(), iters, 12345u + rep);
         cudaEventRecord(ctx->ev1, ctx->stream);
         if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return -1.0;
         float ms = 0;

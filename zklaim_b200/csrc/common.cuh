@@ -46,13 +46,22 @@ struct zkb_ctx {
     std::string err;
     double last_ms = 0.0;
     long launches = 0;
-    // scratch (grow-only); indices are private to each translation unit
-    zkb::DevBuf scratch[24];
+    // scratch (grow-only); slot numbers: enum below
+    zkb::DevBuf scratch[64];
     void *pinned = nullptr; // small pinned staging area for results
     size_t pinned_cap = 0;
 };
 
 namespace zkb {
+
+// scratch slots of a context (G1 and G2 pipelines own disjoint sets so that they may overlap)
+enum {
+    SB_HIST = 0, SB_START, SB_CURSOR, SB_BLOCKSUM, SB_ENT, SB_EBKT, SB_PARTS, SB_BUCKETS, SB_L1, SB_L2, SB_RES,
+    SB_PER_GROUP,                      // slots above are per group: index + group_slot(group)
+    SB_SCAL = 2 * SB_PER_GROUP, SB_PLAIN, SB_STAGE_A, SB_STAGE_B, SB_STAGE_O, SB_MISC,
+    SB_PROVER0 // first slot of prover.cu
+};
+inline int group_slot(int group) { return group == ZKB_G2 ? SB_PER_GROUP : 0; }
 
 extern thread_local std::string g_init_err;
 

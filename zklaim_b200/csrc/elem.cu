@@ -8,7 +8,7 @@
 using namespace zkb;
 
 namespace {
-enum { SB_A = 16, SB_B = 17, SB_O = 18 };
+enum { SB_A = SB_STAGE_A, SB_B = SB_STAGE_B, SB_O = SB_STAGE_O };
 
 template <class F> __global__ void k_field_op(int op, const F *a, const F *b, F *o, size_t n)
 {

@@ -7,15 +7,22 @@
 // serially, adds full-Jacobian points into 2^c buckets and chains c doublings between
 // windows.  This is a different algorithm with the same result (a group element):
 //
+//   0. an MSM *plan* holds up to four queries ("jobs") of one group that are always evaluated
+//      together (for a proving key: A-query, B-query in G1, H- and L-query), and a run
+//      evaluates the plan for a whole batch of proofs at once: one pair list, one sort, one
+//      accumulation launch for all jobs of all proofs;
 //   1. scalars leave Montgomery form once (fp.tcc:228-238) and are cut into W = ceil(255/c)
-//      SIGNED c-bit digits, so a window needs 2^(c-1) buckets;
-//   2. the (point, window) pairs are counting-sorted by bucket: histogram (L2 atomics),
+//      SIGNED c-bit digits, so a window needs 2^(c-1) buckets; zero scalars produce no pair,
+//      scalars equal to one produce a single pair (the reference special-cases both,
+//      multiexp.tcc:466-481);
+//   2. the (item, window) pairs are counting-sorted by bucket: histogram (L2 atomics),
 //      exclusive scan, scatter;
 //   3. bucket accumulation is load-balanced by position, not by bucket: every thread owns a
 //      fixed-length run of the sorted pair list, accumulates it with XYZZ mixed additions and
 //      emits complete buckets directly and at most two boundary partials, which a fix-up pass
-//      merges.  Skewed digit distributions (the 0/1-heavy Groth16 witnesses) cost nothing extra;
-//   4. bases may be stored together with their 2^(j*G*c) multiples (computed once at upload):
+//      merges (warp-cooperatively for buckets that span many runs).  Skewed digit
+//      distributions (the 0/1-heavy Groth16 witnesses) cost nothing extra;
+//   4. bases are stored together with their 2^(j*G*c) multiples (computed once at upload):
 //      windows j*G+g of all j then share bucket set g and no doublings remain at MSM time
 //      when G == 1 -- HBM capacity (180 GB) is traded for the serial doubling chain;
 //   5. the weighted bucket sum  sum_j (j+1) B_j  is a two-level block-parallel suffix scan
@@ -25,6 +32,7 @@
 // gathered point is exactly two / four full 32-byte sectors), copies stored copy-major
 // [F][n]; buckets and partials XYZZ AoS (128 B / 256 B); the pair list is two u32 arrays.
 #include "msm_impl.cuh"
+#include <string.h>
 
 using namespace zkb;
 
@@ -68,39 +76,61 @@ template <class Fn> __device__ __forceinline__ void for_each_digit(const uint32_
     }
 }
 
-__global__ void k_count(const uint32_t *__restrict__ plain, size_t n, int c, int W, int G, uint32_t *__restrict__ hist)
+// item i of proof p: finds its job, loads its plain scalar; returns false when the scalar is zero
+__device__ __forceinline__ bool load_item(const JobTab &tab, const uint32_t *__restrict__ sidx,
+                                          const uint32_t *__restrict__ plain, size_t zstride, uint32_t i, uint32_t p,
+                                          int &job, uint32_t &li, uint32_t *k)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t nb = 1u << (c - 1);
-    uint32_t k[8];
-    const uint4 *p = reinterpret_cast<const uint4 *>(plain + 8 * i);
-    uint4 lo = __ldg(p), hi = __ldg(p + 1);
+    job = 0;
+#pragma unroll
+    for (int q = 1; q < MSM_MAX_JOBS; q++)
+        if (q < (int)tab.njobs && i >= tab.j[q].item_begin) job = q;
+    li = i - tab.j[job].item_begin;
+    const uint32_t si = sidx ? sidx[i] : tab.j[job].scal_first + li;
+    const uint4 *src = reinterpret_cast<const uint4 *>(plain + (size_t)p * zstride + 8 * (size_t)si);
+    const uint4 lo = __ldg(src), hi = __ldg(src + 1);
     k[0] = lo.x; k[1] = lo.y; k[2] = lo.z; k[3] = lo.w; k[4] = hi.x; k[5] = hi.y; k[6] = hi.z; k[7] = hi.w;
-    if ((k[0] | k[1] | k[2] | k[3] | k[4] | k[5] | k[6] | k[7]) == 0) return;
-    for_each_digit(k, c, W, [&](int w, int d) {
+    return (k[0] | k[1] | k[2] | k[3] | k[4] | k[5] | k[6] | k[7]) != 0;
+}
+
+__global__ void k_count(JobTab tab, const uint32_t *__restrict__ sidx, const uint32_t *__restrict__ plain,
+                        size_t zstride, uint32_t *__restrict__ hist)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t p = blockIdx.y;
+    if (i >= tab.n_items) return;
+    int job;
+    uint32_t li, k[8];
+    if (!load_item(tab, sidx, plain, zstride, i, p, job, li, k)) return;
+    const MsmJob J = tab.j[job];
+    const uint32_t nb = 1u << (J.c - 1);
+    uint32_t *h = hist + (size_t)p * tab.Bp + J.bucket_off;
+    for_each_digit(k, J.c, J.W, [&](int w, int d) {
         const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
-        atomicAdd(&hist[(uint32_t)(w % G) * nb + (mag - 1)], 1u);
+        atomicAdd(&h[(uint32_t)(w % J.G) * nb + (mag - 1)], 1u);
     });
 }
 
-__global__ void k_scatter(const uint32_t *__restrict__ plain, size_t n, size_t n_total, size_t offset, int c, int W, int G,
-                          uint32_t *__restrict__ cursor, uint32_t *__restrict__ ent, uint32_t *__restrict__ ebkt)
+__global__ void k_scatter(JobTab tab, const uint32_t *__restrict__ sidx, const uint32_t *__restrict__ plain,
+                          size_t zstride, uint32_t *__restrict__ cursor, uint32_t *__restrict__ ent,
+                          uint32_t *__restrict__ ebkt)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t nb = 1u << (c - 1);
-    uint32_t k[8];
-    const uint4 *p = reinterpret_cast<const uint4 *>(plain + 8 * i);
-    uint4 lo = __ldg(p), hi = __ldg(p + 1);
-    k[0] = lo.x; k[1] = lo.y; k[2] = lo.z; k[3] = lo.w; k[4] = hi.x; k[5] = hi.y; k[6] = hi.z; k[7] = hi.w;
-    if ((k[0] | k[1] | k[2] | k[3] | k[4] | k[5] | k[6] | k[7]) == 0) return;
-    for_each_digit(k, c, W, [&](int w, int d) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t p = blockIdx.y;
+    if (i >= tab.n_items) return;
+    int job;
+    uint32_t li, k[8];
+    if (!load_item(tab, sidx, plain, zstride, i, p, job, li, k)) return;
+    const MsmJob J = tab.j[job];
+    const uint32_t nb = 1u << (J.c - 1);
+    const uint32_t b0 = p * tab.Bp + J.bucket_off;
+    const uint32_t pt0 = J.pts_off + J.base_first + li;
+    for_each_digit(k, J.c, J.W, [&](int w, int d) {
         const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
-        const uint32_t b = (uint32_t)(w % G) * nb + (mag - 1);
+        const uint32_t b = b0 + (uint32_t)(w % J.G) * nb + (mag - 1);
         const uint32_t pos = atomicAdd(&cursor[b], 1u);
-        const uint32_t q = (uint32_t)(w / G);
-        ent[pos] = (uint32_t)(q * n_total + offset + i) | (d < 0 ? 0x80000000u : 0u);
+        const uint32_t q = (uint32_t)(w / J.G);
+        ent[pos] = (pt0 + q * J.n_total) | (d < 0 ? 0x80000000u : 0u);
         ebkt[pos] = b;
     });
 }
@@ -108,10 +138,8 @@ __global__ void k_scatter(const uint32_t *__restrict__ plain, size_t n, size_t n
 // ------------------------------------------------------------------------------------
 // exclusive scan of u32 (three-phase; 2048 elements per block)
 // ------------------------------------------------------------------------------------
-
 __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *sm, uint32_t &total)
 {
-    // warp scan + cross-warp
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t x = v;
 #pragma unroll
@@ -150,7 +178,7 @@ __global__ void k_scan_sums(const uint32_t *__restrict__ in, size_t n, uint32_t 
     if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
 }
 
-// single block: exclusive scan of up to 256*? block sums (sequential chunks of 256)
+// single block: exclusive scan of the block sums (sequential chunks of 256)
 __global__ void k_scan_block_sums(uint32_t *__restrict__ block_sums, unsigned nblocks)
 {
     __shared__ uint32_t sm[32];
@@ -165,7 +193,7 @@ __global__ void k_scan_block_sums(uint32_t *__restrict__ block_sums, unsigned nb
     }
 }
 
-// out[i] = exclusive prefix; out[n] = total.  `out2` (optional) receives a second copy of out[0..n).
+// out[i] = exclusive prefix; out[n] = total.  `out2` receives a second copy of out[0..n).
 __global__ void k_scan_final(const uint32_t *__restrict__ in, size_t n, const uint32_t *__restrict__ block_sums,
                              uint32_t *__restrict__ out, uint32_t *__restrict__ out2)
 {
@@ -191,39 +219,106 @@ __global__ void k_scan_final(const uint32_t *__restrict__ in, size_t n, const ui
     }
 }
 
-
 } // namespace
 
 namespace zkb {
 
-int msm_sort_pairs(zkb_ctx *ctx, const zkb_bases *b, size_t offset, const Fr *d_scalars, size_t n)
+int msm_choose_c(size_t n_eff, int group, int precompute_factor)
+{
+    // cost in base-field multiplications: XYZZ mixed add 10 (G1) / 30 (G2), full add 14 / 42
+    const double madd = group == ZKB_G2 ? 30 : 10, add = group == ZKB_G2 ? 42 : 14, dbl = group == ZKB_G2 ? 27 : 9;
+    int best = 4;
+    double best_cost = 1e300;
+    for (int c = 4; c <= 16; c++) {
+        const int W = (255 + c - 1) / c;
+        int F = precompute_factor <= 0 ? W : precompute_factor;
+        if (F > W) F = W;
+        const int G = (W + F - 1) / F;
+        const double cost = (double)n_eff * W * madd + (double)G * (double)(1u << c) * add + (double)(G - 1) * c * dbl * 64;
+        if (cost < best_cost) {
+            best_cost = cost;
+            best = c;
+        }
+    }
+    return best;
+}
+
+int plan_add_job(zkb_ctx *ctx, MsmPlan *plan, size_t n_total, int c, int precompute_factor)
+{
+    JobTab &t = plan->tab;
+    if (t.njobs >= MSM_MAX_JOBS) return fail(ctx, ZKB_ERR_ARG, "msm plan: too many jobs");
+    if (c < 2 || c > 16) return fail(ctx, ZKB_ERR_ARG, "msm plan: window bits must be 2..16");
+    MsmJob &J = t.j[t.njobs];
+    const int W = (255 + c - 1) / c;
+    int F = precompute_factor <= 0 ? W : precompute_factor;
+    if (F > W) F = W;
+    const int G = (W + F - 1) / F;
+    F = (W + G - 1) / G;
+    const double pts = (double)plan->pts_count + (double)n_total * F;
+    if (pts >= 2147483648.0 || (double)t.n_items + (double)n_total >= 4294967295.0)
+        return fail(ctx, ZKB_ERR_ARG, "msm plan: n * precomputed copies exceeds 2^31 points");
+    J.item_begin = t.n_items;
+    J.n = (uint32_t)n_total;
+    J.base_first = 0;
+    J.n_total = (uint32_t)n_total;
+    J.pts_off = (uint32_t)plan->pts_count;
+    J.scal_first = t.n_items;
+    J.bucket_off = t.Bp;
+    J.c = (uint16_t)c;
+    J.W = (uint16_t)W;
+    J.G = (uint16_t)G;
+    J.F = (uint16_t)F;
+    t.n_items += (uint32_t)n_total;
+    t.Bp += (uint32_t)G << (c - 1);
+    t.njobs++;
+    plan->pts_count += n_total * (size_t)F;
+    return ZKB_OK;
+}
+
+int plan_alloc(zkb_ctx *ctx, MsmPlan *plan)
+{
+    const size_t psz = plan->group == ZKB_G2 ? sizeof(Affine<Fq2>) : sizeof(Affine<Fq>);
+    plan->dev = ctx->dev;
+    plan->bytes = plan->pts_count * psz;
+    ZKB_CUDA(ctx, cudaMalloc(&plan->d_pts, plan->bytes ? plan->bytes : 16));
+    return ZKB_OK;
+}
+
+void plan_free(MsmPlan *plan)
+{
+    if (plan->d_pts) cudaFree(plan->d_pts);
+    if (plan->d_sidx) cudaFree(plan->d_sidx);
+    plan->d_pts = nullptr;
+    plan->d_sidx = nullptr;
+}
+
+int msm_sort_pairs(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t *d_plain, size_t zstride,
+                   int batch)
 {
     cudaStream_t st = ctx->stream;
-    const int c = b->c, W = b->W, G = b->G;
-    const uint32_t nb = 1u << (c - 1);
-    const uint32_t B = nb * (uint32_t)G;
-    const size_t Emax = n * (size_t)W;
-    if (Emax >= (1ull << 32)) return fail(ctx, ZKB_ERR_ARG, "msm: n * windows exceeds 2^32 pairs");
-    const unsigned scan_blocks = ceil_div((size_t)B, SCAN_BLK);
-    ZKB_CUDA(ctx, ctx->scratch[SB_PLAIN].ensure(n * 32));
-    ZKB_CUDA(ctx, ctx->scratch[SB_HIST].ensure((size_t)B * 4));
-    ZKB_CUDA(ctx, ctx->scratch[SB_START].ensure(((size_t)B + 1) * 4));
-    ZKB_CUDA(ctx, ctx->scratch[SB_CURSOR].ensure((size_t)B * 4));
-    ZKB_CUDA(ctx, ctx->scratch[SB_BLOCKSUM].ensure((size_t)scan_blocks * 4 + 16));
-    ZKB_CUDA(ctx, ctx->scratch[SB_ENT].ensure(Emax * 4 + 16));
-    ZKB_CUDA(ctx, ctx->scratch[SB_EBKT].ensure(Emax * 4 + 16));
-    uint32_t *plain = ctx->scratch[SB_PLAIN].as<uint32_t>();
-    uint32_t *hist = ctx->scratch[SB_HIST].as<uint32_t>();
-    uint32_t *start = ctx->scratch[SB_START].as<uint32_t>();
-    uint32_t *cursor = ctx->scratch[SB_CURSOR].as<uint32_t>();
-    uint32_t *bsum = ctx->scratch[SB_BLOCKSUM].as<uint32_t>();
-    uint32_t *ent = ctx->scratch[SB_ENT].as<uint32_t>();
-    uint32_t *ebkt = ctx->scratch[SB_EBKT].as<uint32_t>();
+    const int gs = group_slot(plan->group);
+    size_t Emax = 0;
+    for (uint32_t q = 0; q < tab.njobs; q++) Emax += (size_t)tab.j[q].n * tab.j[q].W;
+    Emax *= (size_t)batch;
+    const size_t B = (size_t)tab.Bp * batch;
+    if (Emax >= (1ull << 32) || B >= (1ull << 32)) return fail(ctx, ZKB_ERR_ARG, "msm: more than 2^32 pairs in one run");
+    const unsigned scan_blocks = ceil_div(B, SCAN_BLK);
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_HIST].ensure(B * 4));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_START].ensure((B + 1) * 4));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_CURSOR].ensure(B * 4));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_BLOCKSUM].ensure((size_t)scan_blocks * 4 + 16));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_ENT].ensure(Emax * 4 + 16));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_EBKT].ensure(Emax * 4 + 16));
+    uint32_t *hist = ctx->scratch[gs + SB_HIST].as<uint32_t>();
+    uint32_t *start = ctx->scratch[gs + SB_START].as<uint32_t>();
+    uint32_t *cursor = ctx->scratch[gs + SB_CURSOR].as<uint32_t>();
+    uint32_t *bsum = ctx->scratch[gs + SB_BLOCKSUM].as<uint32_t>();
+    uint32_t *ent = ctx->scratch[gs + SB_ENT].as<uint32_t>();
+    uint32_t *ebkt = ctx->scratch[gs + SB_EBKT].as<uint32_t>();
 
-    ZKB_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t)B * 4, st));
-    k_to_plain<<<ceil_div(n, 128), 128, 0, st>>>(d_scalars, (Fr *)plain, n);
-    ZKB_LAUNCH_CHECK(ctx);
-    k_count<<<ceil_div(n, 128), 128, 0, st>>>(plain, n, c, W, G, hist);
+    ZKB_CUDA(ctx, cudaMemsetAsync(hist, 0, B * 4, st));
+    const dim3 grid(ceil_div(tab.n_items, 128), (unsigned)batch);
+    k_count<<<grid, 128, 0, st>>>(tab, plan->d_sidx, d_plain, zstride, hist);
     ZKB_LAUNCH_CHECK(ctx);
     k_scan_sums<<<scan_blocks, SCAN_T, 0, st>>>(hist, B, bsum);
     ZKB_LAUNCH_CHECK(ctx);
@@ -231,44 +326,50 @@ int msm_sort_pairs(zkb_ctx *ctx, const zkb_bases *b, size_t offset, const Fr *d_
     ZKB_LAUNCH_CHECK(ctx);
     k_scan_final<<<scan_blocks, SCAN_T, 0, st>>>(hist, B, bsum, start, cursor);
     ZKB_LAUNCH_CHECK(ctx);
-    k_scatter<<<ceil_div(n, 128), 128, 0, st>>>(plain, n, b->n, offset, c, W, G, cursor, ent, ebkt);
+    k_scatter<<<grid, 128, 0, st>>>(tab, plan->d_sidx, d_plain, zstride, cursor, ent, ebkt);
     ZKB_LAUNCH_CHECK(ctx);
     return ZKB_OK;
 }
 
 template <class F>
-static int msm_run(zkb_ctx *ctx, const zkb_bases *b, size_t offset, const Fr *d_scalars, size_t n, uint64_t *out_host)
+int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t *d_plain, size_t zstride, int batch,
+            XYZZ<F> *d_res)
 {
     typedef XYZZ<F> PT;
-    const uint32_t nb = 1u << (b->c - 1);
-    const uint32_t B = nb * (uint32_t)b->G;
-    const size_t Emax = n * (size_t)b->W;
+    const int gs = group_slot(plan->group);
+    if (batch <= 0 || batch > 65535) return fail(ctx, ZKB_ERR_ARG, "msm: batch must be 1..65535");
+    size_t Emax = 0;
+    for (uint32_t q = 0; q < tab.njobs; q++) Emax += (size_t)tab.j[q].n * tab.j[q].W;
+    Emax *= (size_t)batch;
+    const size_t B = (size_t)tab.Bp * batch;
     const uint32_t S = msm_run_length(ctx, Emax);
     const size_t runs = (Emax + S - 1) / S;
-    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    int rc = msm_sort_pairs(ctx, b, offset, d_scalars, n);
+    int rc = msm_sort_pairs(ctx, plan, tab, d_plain, zstride, batch);
     if (rc) return rc;
-    ZKB_CUDA(ctx, ctx->scratch[SB_PARTS].ensure(2 * runs * sizeof(PT)));
-    ZKB_CUDA(ctx, ctx->scratch[SB_BUCKETS].ensure((size_t)B * sizeof(PT)));
-    rc = launch_accumulate<F>(ctx, (const Affine<F> *)b->d_pts, ctx->scratch[SB_ENT].as<uint32_t>(),
-                              ctx->scratch[SB_EBKT].as<uint32_t>(), ctx->scratch[SB_START].as<uint32_t>(), B, S,
-                              ctx->scratch[SB_BUCKETS].as<PT>(), ctx->scratch[SB_PARTS].as<PT>(), runs);
-    if (rc) return rc;
-    return msm_finish<F>(ctx, b, n, S, out_host);
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_PARTS].ensure(2 * (runs + 1) * sizeof(PT)));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_BUCKETS].ensure(B * sizeof(PT)));
+    if (runs) {
+        rc = launch_accumulate<F>(ctx, (const Affine<F> *)plan->d_pts, ctx->scratch[gs + SB_ENT].as<uint32_t>(),
+                                  ctx->scratch[gs + SB_EBKT].as<uint32_t>(), ctx->scratch[gs + SB_START].as<uint32_t>(),
+                                  (uint32_t)B, S, ctx->scratch[gs + SB_BUCKETS].as<PT>(),
+                                  ctx->scratch[gs + SB_PARTS].as<PT>(), runs);
+        if (rc) return rc;
+    }
+    return msm_finish<F>(ctx, plan, tab, batch, S, d_res);
 }
+
+int msm_to_plain(zkb_ctx *ctx, const void *d_mont, uint32_t *d_plain, size_t n)
+{
+    if (!n) return ZKB_OK;
+    k_to_plain<<<ceil_div(n, 128), 128, 0, ctx->stream>>>((const Fr *)d_mont, (Fr *)d_plain, n);
+    ZKB_LAUNCH_CHECK(ctx);
+    return ZKB_OK;
+}
+
+template int msm_run<Fq>(zkb_ctx *, const MsmPlan *, const JobTab &, const uint32_t *, size_t, int, XYZZ<Fq> *);
+template int msm_run<Fq2>(zkb_ctx *, const MsmPlan *, const JobTab &, const uint32_t *, size_t, int, XYZZ<Fq2> *);
 
 } // namespace zkb
-
-namespace {
-int ilog2_floor(size_t x)
-{
-    int l = 0;
-    while (x >>= 1) l++;
-    return l;
-}
-
-
-} // namespace
 
 extern "C" {
 
@@ -277,35 +378,19 @@ int zkb_bases_upload(zkb_ctx *ctx, int group, const uint64_t *affine, size_t n, 
 {
     if (!ctx || !affine || !out || n == 0 || (group != ZKB_G1 && group != ZKB_G2))
         return fail(ctx, ZKB_ERR_ARG, "zkb_bases_upload: bad argument");
-    if (window_bits < 0 || window_bits > 16 || precompute_factor < 0)
-        return fail(ctx, ZKB_ERR_ARG, "zkb_bases_upload: window_bits must be 0..16");
+    if (window_bits < 0 || window_bits > 16 || window_bits == 1 || precompute_factor < 0)
+        return fail(ctx, ZKB_ERR_ARG, "zkb_bases_upload: window_bits must be 0 or 2..16");
     ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
     zkb_bases *b = new zkb_bases();
-    b->group = group;
-    b->dev = ctx->dev;
+    b->plan.group = group;
     b->n = n;
-    int c = window_bits;
-    if (c == 0) {
-        const int lg = ilog2_floor(n);
-        c = lg - (precompute_factor == 1 ? 4 : 1);
-        if (group == ZKB_G2) c -= 1;
-        if (c > 16) c = 16;
-        if (c < 4) c = 4;
-    }
-    if (c < 2) c = 2;
-    b->c = c;
-    b->W = (255 + c - 1) / c;
-    int F = precompute_factor == 0 ? b->W : precompute_factor;
-    if (F > b->W) F = b->W;
-    b->G = (b->W + F - 1) / F;
-    b->F = (b->W + b->G - 1) / b->G;
-    if ((double)n * b->F >= 2147483648.0) {
-        delete b;
-        return fail(ctx, ZKB_ERR_ARG, "zkb_bases_upload: n * precompute_factor exceeds 2^31");
-    }
-    int rc = group == ZKB_G1 ? bases_build<Fq>(ctx, b, affine) : bases_build<Fq2>(ctx, b, affine);
+    const int c = window_bits ? window_bits : msm_choose_c(n, group, precompute_factor);
+    int rc = plan_add_job(ctx, &b->plan, n, c, precompute_factor);
+    if (!rc) rc = plan_alloc(ctx, &b->plan);
+    if (!rc) rc = group == ZKB_G1 ? plan_upload_job<Fq>(ctx, &b->plan, 0, affine) : plan_upload_job<Fq2>(ctx, &b->plan, 0, affine);
+    if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(ctx, ZKB_ERR_CUDA, "zkb_bases_upload: precomputation failed");
     if (rc) {
-        if (b->d_pts) cudaFree(b->d_pts);
+        plan_free(&b->plan);
         delete b;
         return rc;
     }
@@ -316,28 +401,46 @@ int zkb_bases_upload(zkb_ctx *ctx, int group, const uint64_t *affine, size_t n, 
 void zkb_bases_free(zkb_bases *b)
 {
     if (!b) return;
-    if (b->d_pts) cudaFree(b->d_pts);
+    plan_free(&b->plan);
     delete b;
 }
 
-size_t zkb_bases_device_bytes(const zkb_bases *b) { return b ? b->bytes : 0; }
+size_t zkb_bases_device_bytes(const zkb_bases *b) { return b ? b->plan.bytes : 0; }
 
 int zkb_msm_device(zkb_ctx *ctx, const zkb_bases *bases, size_t offset, const void *d_scalars, size_t n, uint64_t *out)
 {
     if (!ctx || !bases || !out || (!d_scalars && n)) return fail(ctx, ZKB_ERR_ARG, "zkb_msm: bad argument");
     if (offset + n > bases->n) return fail(ctx, ZKB_ERR_ARG, "zkb_msm: range exceeds the uploaded bases");
     ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    const bool g1 = bases->plan.group == ZKB_G1;
     if (n == 0) {
         // empty sum = the reference's zero (0, 1, 0)  (alt_bn128_init.cpp:145-147)
-        const size_t limbs = bases->group == ZKB_G1 ? 12 : 24;
-        memset(out, 0, limbs * 8);
+        memset(out, 0, (g1 ? 12 : 24) * 8);
         const uint64_t one_q[4] = {0xd35d438dc58f0d9dull, 0x0a78eb28f5c70b3dull, 0x666ea36f7879462cull,
                                    0x0e0a77c19a07df2full};
-        memcpy(out + (bases->group == ZKB_G1 ? 4 : 8), one_q, 32);
+        memcpy(out + (g1 ? 4 : 8), one_q, 32);
         return ZKB_OK;
     }
-    if (bases->group == ZKB_G1) return msm_run<Fq>(ctx, bases, offset, (const Fr *)d_scalars, n, out);
-    return msm_run<Fq2>(ctx, bases, offset, (const Fr *)d_scalars, n, out);
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    ZKB_CUDA(ctx, ctx->scratch[SB_PLAIN].ensure(n * 32));
+    uint32_t *plain = ctx->scratch[SB_PLAIN].as<uint32_t>();
+    int rc = msm_to_plain(ctx, d_scalars, plain, n);
+    if (rc) return rc;
+    JobTab tab = bases->plan.tab;
+    tab.j[0].n = (uint32_t)n;
+    tab.j[0].base_first = (uint32_t)offset;
+    tab.j[0].scal_first = 0;
+    tab.n_items = (uint32_t)n;
+    const int gs = group_slot(bases->plan.group);
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_RES].ensure(g1 ? sizeof(G1X) : sizeof(G2X)));
+    if (g1) {
+        rc = msm_run<Fq>(ctx, &bases->plan, tab, plain, 0, 1, ctx->scratch[gs + SB_RES].as<G1X>());
+        if (!rc) rc = results_to_host<Fq>(ctx, ctx->scratch[gs + SB_RES].as<G1X>(), 1, out);
+    } else {
+        rc = msm_run<Fq2>(ctx, &bases->plan, tab, plain, 0, 1, ctx->scratch[gs + SB_RES].as<G2X>());
+        if (!rc) rc = results_to_host<Fq2>(ctx, ctx->scratch[gs + SB_RES].as<G2X>(), 1, out);
+    }
+    return rc;
 }
 
 int zkb_msm(zkb_ctx *ctx, const zkb_bases *bases, size_t offset, const uint64_t *scalars, size_t n, uint64_t *out)

@@ -4,29 +4,6 @@
 #include "msm_impl.cuh"
 
 namespace zkb {
-// merges the boundary partials of every bucket that spans more than one run; empty buckets -> infinity
-template <class F>
-__global__ void __launch_bounds__(128)
-k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__restrict__ buckets,
-        const XYZZ<F> *__restrict__ parts)
-{
-    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
-    const uint32_t s = start[b], e = start[b + 1];
-    if (s == e) {
-        st_vec(buckets + b, XYZZ<F>::inf());
-        return;
-    }
-    const uint32_t t0 = s / S, t1 = (e - 1) / S;
-    if (t0 == t1) return; // complete inside one run: already written
-    XYZZ<F> acc = ld_vec(parts + 2 * (size_t)t0 + ((s == t0 * S) ? 0 : 1));
-    for (uint32_t t = t0 + 1; t <= t1; t++) acc.add(ld_vec(parts + 2 * (size_t)t));
-    st_vec(buckets + b, acc);
-}
-
-// ------------------------------------------------------------------------------------
-// weighted bucket sum  R = sum_j (j+1) * E_j  via block-parallel suffix scans
-// ------------------------------------------------------------------------------------
 // word-striped shared-memory staging (conflict-free for any struct size)
 template <class PT> __device__ __forceinline__ void sm_put(uint32_t *sm, int T, int t, const PT &v)
 {
@@ -43,6 +20,71 @@ template <class PT> __device__ __forceinline__ PT sm_get(const uint32_t *sm, int
     return v;
 }
 
+// merges the boundary partials of every bucket that spans more than one run; empty buckets -> infinity.
+// One lane per bucket for short spans; a bucket that spans many runs (the "scalar == 1" bucket of a
+// Groth16 witness holds thousands of pairs) is reduced by its whole warp.
+constexpr int FIXUP_T = 128, FIXUP_WIDE = 64;
+template <class F>
+__global__ void __launch_bounds__(FIXUP_T)
+k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__restrict__ buckets,
+        const XYZZ<F> *__restrict__ parts)
+{
+    extern __shared__ uint32_t sm[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t *wsm = sm + (size_t)wid * 32 * (sizeof(XYZZ<F>) / 4);
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t s = 0, e = 0;
+    if (b < B) {
+        s = start[b];
+        e = start[b + 1];
+    }
+    uint32_t t0 = 0, t1 = 0;
+    bool multi = false;
+    if (b < B) {
+        if (s == e) {
+            st_vec(buckets + b, XYZZ<F>::inf());
+        } else {
+            t0 = s / S;
+            t1 = (e - 1) / S;
+            multi = t1 > t0;
+        }
+    }
+    const bool wide = multi && (t1 - t0) >= FIXUP_WIDE;
+    if (multi && !wide) {
+        XYZZ<F> acc = ld_vec(parts + 2 * (size_t)t0 + ((s == t0 * S) ? 0 : 1));
+        for (uint32_t t = t0 + 1; t <= t1; t++) acc.add(ld_vec(parts + 2 * (size_t)t));
+        st_vec(buckets + b, acc);
+    }
+    unsigned todo = __ballot_sync(0xffffffffu, wide);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint32_t ws = __shfl_sync(0xffffffffu, s, src);
+        const uint32_t wt0 = __shfl_sync(0xffffffffu, t0, src), wt1 = __shfl_sync(0xffffffffu, t1, src);
+        const uint32_t wb = __shfl_sync(0xffffffffu, b, src);
+        // partial k of the span: k = 0 is the head partial of run t0, k >= 1 the head partial of run t0 + k
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (uint32_t t = wt0 + lane; t <= wt1; t += 32) {
+            const size_t idx = (t == wt0) ? 2 * (size_t)t + ((ws == t * S) ? 0 : 1) : 2 * (size_t)t;
+            acc.add(ld_vec(parts + idx));
+        }
+        sm_put(wsm, 32, lane, acc);
+        __syncwarp();
+        for (int d = 16; d > 0; d >>= 1) {
+            if (lane < d) {
+                acc.add(sm_get<XYZZ<F>>(wsm, 32, lane + d));
+                sm_put(wsm, 32, lane, acc);
+            }
+            __syncwarp();
+        }
+        if (lane == 0) st_vec(buckets + wb, acc);
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// weighted bucket sum  R = sum_j (j+1) * E_j  via block-parallel suffix scans
+// ------------------------------------------------------------------------------------
 // inclusive suffix scan over the block: v_t <- sum_{u >= t} v_u
 template <class PT> __device__ __forceinline__ void block_suffix_scan(uint32_t *sm, int T, int t, PT &v)
 {
@@ -74,15 +116,18 @@ template <class PT> __device__ __forceinline__ void block_sum(uint32_t *sm, int 
     }
 }
 
-// level 1: block handles T*L consecutive buckets of one set; out[blk] = (R_blk, S_blk)
+// level 1: block handles T*L consecutive buckets of one set; out[set][blk] = (R_blk, S_blk).
+// set = blockIdx.y = proof * G + g; its buckets start at proof * Bp + bucket_off + g * nb.
 template <class F>
 __global__ void __launch_bounds__(128)
-k_reduce_l1(const XYZZ<F> *__restrict__ buckets, uint32_t nb, int L, int logL, XYZZ<F> *__restrict__ out)
+k_reduce_l1(const XYZZ<F> *__restrict__ buckets, uint32_t Bp, uint32_t bucket_off, uint32_t G, uint32_t nb, int L,
+            int logL, XYZZ<F> *__restrict__ out)
 {
     extern __shared__ uint32_t sm[];
     const int T = blockDim.x, t = threadIdx.x;
     const uint32_t set = blockIdx.y;
-    const XYZZ<F> *E = buckets + (size_t)set * nb + ((size_t)blockIdx.x * T + t) * L;
+    const size_t base = (size_t)(set / G) * Bp + bucket_off + (size_t)(set % G) * nb;
+    const XYZZ<F> *E = buckets + base + ((size_t)blockIdx.x * T + t) * L;
     XYZZ<F> acc = XYZZ<F>::inf(), tot = XYZZ<F>::inf();
     for (int u = L - 1; u >= 0; u--) {
         acc.add(ld_vec(E + u));
@@ -114,8 +159,6 @@ k_reduce_l2(const XYZZ<F> *__restrict__ l1, int NB, int logCH, XYZZ<F> *__restri
     const int T = blockDim.x, t = threadIdx.x;
     const uint32_t set = blockIdx.x;
     XYZZ<F> R = XYZZ<F>::inf(), S = XYZZ<F>::inf();
-    // threads stride over level-1 blocks when NB > T: fold serially first (weights handled below)
-    // (NB <= T is guaranteed by the host-side choice of L; kept simple)
     if (t < NB) {
         R = ld_vec(l1 + 2 * ((size_t)set * NB + t));
         S = ld_vec(l1 + 2 * ((size_t)set * NB + t) + 1);
@@ -132,16 +175,27 @@ k_reduce_l2(const XYZZ<F> *__restrict__ l1, int NB, int logCH, XYZZ<F> *__restri
     }
 }
 
-// Horner over the G bucket sets: res = sum_g 2^(g*c) R_g ; writes the reference's Jacobian layout
-template <class F> __global__ void k_final(const XYZZ<F> *__restrict__ sets, int G, int c, Jacobian<F> *__restrict__ out)
+// Horner over the G bucket sets of every proof: res[p * njobs + job] = sum_g 2^(g*c) R_{p,g}
+template <class F>
+__global__ void k_final(const XYZZ<F> *__restrict__ sets, int batch, int G, int c, int njobs, int job,
+                        XYZZ<F> *__restrict__ res)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    XYZZ<F> res = ld_vec(sets + (G - 1));
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= batch) return;
+    const XYZZ<F> *s = sets + (size_t)p * G;
+    XYZZ<F> r = ld_vec(s + (G - 1));
     for (int g = G - 2; g >= 0; g--) {
-        for (int i = 0; i < c; i++) res = res.dbl();
-        res.add(ld_vec(sets + g));
+        for (int i = 0; i < c; i++) r = r.dbl();
+        r.add(ld_vec(s + g));
     }
-    st_vec(out, res.to_jacobian());
+    st_vec(res + (size_t)p * njobs + job, r);
+}
+
+template <class F> __global__ void k_to_jacobian(const XYZZ<F> *__restrict__ in, Jacobian<F> *__restrict__ out, size_t n)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    st_vec(out + i, ld_vec(in + i).to_jacobian());
 }
 
 // ------------------------------------------------------------------------------------
@@ -169,73 +223,80 @@ k_next_copy(const Affine<F> *__restrict__ prev, Affine<F> *__restrict__ next, si
     st_vec(next + i, r);
 }
 
-
-template <class F> int msm_finish(zkb_ctx *ctx, const zkb_bases *b, size_t n, uint32_t S, uint64_t *out_host)
+template <class F> int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t S, XYZZ<F> *d_res)
 {
     typedef XYZZ<F> PT;
     cudaStream_t st = ctx->stream;
-    const int c = b->c, G = b->G;
-    const uint32_t nb = 1u << (c - 1);
-    const uint32_t B = nb * (uint32_t)G;
-    (void)n;
-    // level-1 reduction geometry: nb = NB * T * L
-    const int T = (int)(nb < 128 ? nb : 128);
-    int L = (int)(nb / T);
-    if (L > 8) L = 8;
-    const int NB = (int)(nb / ((uint32_t)T * L));
-    if (NB > 128) return fail(ctx, ZKB_ERR_ARG, "msm: window too wide for the bucket reduction");
-    int T2 = 1;
-    while (T2 < NB) T2 <<= 1;
-    ZKB_CUDA(ctx, ctx->scratch[SB_L1].ensure((size_t)2 * G * NB * sizeof(PT)));
-    ZKB_CUDA(ctx, ctx->scratch[SB_L2].ensure((size_t)G * sizeof(PT)));
-    ZKB_CUDA(ctx, ctx->scratch[SB_OUT].ensure(sizeof(Jacobian<F>)));
-    if (ensure_pinned(ctx, sizeof(Jacobian<F>))) return ZKB_ERR_CUDA;
-    uint32_t *start = ctx->scratch[SB_START].as<uint32_t>();
-    PT *parts = ctx->scratch[SB_PARTS].as<PT>();
-    PT *buckets = ctx->scratch[SB_BUCKETS].as<PT>();
-    PT *l1 = ctx->scratch[SB_L1].as<PT>();
-    PT *l2 = ctx->scratch[SB_L2].as<PT>();
-    Jacobian<F> *d_out = ctx->scratch[SB_OUT].as<Jacobian<F>>();
+    const int gs = group_slot(plan->group);
+    const size_t B = (size_t)tab.Bp * batch;
+    uint32_t *start = ctx->scratch[gs + SB_START].as<uint32_t>();
+    PT *parts = ctx->scratch[gs + SB_PARTS].as<PT>();
+    PT *buckets = ctx->scratch[gs + SB_BUCKETS].as<PT>();
+    k_fixup<F><<<ceil_div(B, FIXUP_T), FIXUP_T, (FIXUP_T / 32) * 32 * sizeof(PT), st>>>(start, (uint32_t)B, S, buckets, parts);
+    ZKB_LAUNCH_CHECK(ctx);
+    for (uint32_t q = 0; q < tab.njobs; q++) {
+        const MsmJob &J = tab.j[q];
+        const uint32_t nb = 1u << (J.c - 1);
+        // level-1 reduction geometry: nb = NB * T * L
+        const int T = (int)(nb < 128 ? nb : 128);
+        int L = (int)(nb / T);
+        if (L > 8) L = 8;
+        const int NB = (int)(nb / ((uint32_t)T * L));
+        if (NB > 128) return fail(ctx, ZKB_ERR_ARG, "msm: window too wide for the bucket reduction");
+        int T2 = 1;
+        while (T2 < NB) T2 <<= 1;
+        const size_t sets = (size_t)batch * J.G;
+        if (sets > 65535) return fail(ctx, ZKB_ERR_ARG, "msm: batch * bucket sets exceeds 65535");
+        ZKB_CUDA(ctx, ctx->scratch[gs + SB_L1].ensure(2 * sets * NB * sizeof(PT)));
+        ZKB_CUDA(ctx, ctx->scratch[gs + SB_L2].ensure(sets * sizeof(PT)));
+        PT *l1 = ctx->scratch[gs + SB_L1].as<PT>();
+        PT *l2 = ctx->scratch[gs + SB_L2].as<PT>();
+        int logL = 0;
+        while ((1 << logL) < L) logL++;
+        k_reduce_l1<F><<<dim3(NB, (unsigned)sets), T, (size_t)T * sizeof(PT), st>>>(buckets, tab.Bp, J.bucket_off, J.G, nb, L,
+                                                                                   logL, l1);
+        ZKB_LAUNCH_CHECK(ctx);
+        int logCH = 0;
+        while ((1u << logCH) < (uint32_t)T * L) logCH++;
+        k_reduce_l2<F><<<(unsigned)sets, T2, (size_t)T2 * sizeof(PT), st>>>(l1, NB, logCH, l2);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_final<F><<<ceil_div((size_t)batch, 32), 32, 0, st>>>(l2, batch, J.G, J.c, (int)tab.njobs, (int)q, d_res);
+        ZKB_LAUNCH_CHECK(ctx);
+    }
+    return ZKB_OK;
+}
 
-    k_fixup<F><<<ceil_div((size_t)B, 128), 128, 0, st>>>(start, B, S, buckets, parts);
-    ZKB_LAUNCH_CHECK(ctx);
-    int logL = 0;
-    while ((1 << logL) < L) logL++;
-    k_reduce_l1<F><<<dim3(NB, G), T, (size_t)T * sizeof(PT), st>>>(buckets, nb, L, logL, l1);
-    ZKB_LAUNCH_CHECK(ctx);
-    int logCH = 0;
-    while ((1u << logCH) < (uint32_t)T * L) logCH++;
-    k_reduce_l2<F><<<G, T2, (size_t)T2 * sizeof(PT), st>>>(l1, NB, logCH, l2);
-    ZKB_LAUNCH_CHECK(ctx);
-    k_final<F><<<1, 32, 0, st>>>(l2, G, c, d_out);
+template <class F> int results_to_host(zkb_ctx *ctx, const XYZZ<F> *d_res, size_t count, uint64_t *out_jacobian)
+{
+    cudaStream_t st = ctx->stream;
+    const size_t bytes = count * sizeof(Jacobian<F>);
+    ZKB_CUDA(ctx, ctx->scratch[SB_STAGE_O].ensure(bytes));
+    if (ensure_pinned(ctx, bytes)) return ZKB_ERR_CUDA;
+    Jacobian<F> *d_out = ctx->scratch[SB_STAGE_O].as<Jacobian<F>>();
+    k_to_jacobian<F><<<ceil_div(count, 64), 64, 0, st>>>(d_res, d_out, count);
     ZKB_LAUNCH_CHECK(ctx);
     ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
-    ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_out, sizeof(Jacobian<F>), cudaMemcpyDeviceToHost, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_out, bytes, cudaMemcpyDeviceToHost, st));
     ZKB_CUDA(ctx, cudaStreamSynchronize(st));
     float ms = 0;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_ms = ms;
-    memcpy(out_host, ctx->pinned, sizeof(Jacobian<F>));
+    memcpy(out_jacobian, ctx->pinned, bytes);
     return ZKB_OK;
 }
 
-template <class F>
-int bases_build(zkb_ctx *ctx, zkb_bases *b, const uint64_t *affine_host)
+// uploads the bases of one job (copy 0) and derives the other copies on the device (asynchronous on the stream)
+template <class F> int plan_upload_job(zkb_ctx *ctx, MsmPlan *plan, int job, const uint64_t *affine_host)
 {
-    const size_t n = b->n;
-    const size_t one = n * sizeof(Affine<F>);
-    ZKB_CUDA(ctx, cudaMalloc(&b->d_pts, one * b->F));
-    b->bytes = one * b->F;
-    ZKB_CUDA(ctx, cudaMemcpyAsync(b->d_pts, affine_host, one, cudaMemcpyHostToDevice, ctx->stream));
-    Affine<F> *p = (Affine<F> *)b->d_pts;
-    for (int q = 1; q < b->F; q++) {
-        k_next_copy<F><<<ceil_div(n, 128), 128, 0, ctx->stream>>>(p + (size_t)(q - 1) * n, p + (size_t)q * n, n,
-                                                                  b->G * b->c);
+    const MsmJob &J = plan->tab.j[job];
+    const size_t n = J.n_total;
+    Affine<F> *p = (Affine<F> *)plan->d_pts + J.pts_off;
+    ZKB_CUDA(ctx, cudaMemcpyAsync(p, affine_host, n * sizeof(Affine<F>), cudaMemcpyHostToDevice, ctx->stream));
+    for (int q = 1; q < J.F; q++) {
+        k_next_copy<F><<<ceil_div(n, 128), 128, 0, ctx->stream>>>(p + (size_t)(q - 1) * n, p + (size_t)q * n, n, J.G * J.c);
         ZKB_LAUNCH_CHECK(ctx);
     }
-    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return ZKB_OK;
 }
-
 
 } // namespace zkb
