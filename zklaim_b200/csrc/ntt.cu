@@ -1,0 +1,579 @@
+// ntt.cu -- number-theoretic transforms over alt_bn128 Fr and libfqfft's evaluation domains for sm_100a.
+//
+// Replaces, on the prover path, libfqfft's basic_radix2_domain and step_radix2_domain
+// (libfqfft/evaluation_domain/domains/basic_radix2_domain.tcc:41-112, basic_radix2_domain_aux.tcc:45-79,
+// :172-180, step_radix2_domain.tcc:21-248) and the domain factory
+// (get_evaluation_domain.tcc:33-52).  The reference runs a serial in-place radix-2 DIT with an
+// explicit bit-reversal.  Field arithmetic is exact, so any schedule that evaluates the same
+// DFT gives bit-identical vectors; the schedule here is chosen for the GPU:
+//
+//   * a transform of size 2^L is cut into passes of at most 8 butterfly levels; a thread block
+//     stages C columns x 2^k elements in shared memory (word-planar, conflict-free), runs the
+//     k levels there and writes back in place, so one pass costs one HBM read and one write
+//     of the vector, in 256-byte rows;
+//   * the witness map needs iFFT followed by cosetFFT: the inverse runs decimation-in-
+//     frequency (natural in, bit-reversed out), the coset scaling is applied in bit-reversed
+//     order (folded into the last pass), and the forward transform runs decimation-in-time
+//     (bit-reversed in, natural out), so no permutation pass exists on that path;
+//   * all transforms are batched over vectors (the A, B, C polynomials of a whole batch of
+//     proofs go through one launch per pass).
+//
+// Twiddles w^i, i < n/2 are tabulated once per domain in HBM (L2-resident for the sizes of
+// the zklaim circuit).
+#include "ntt.cuh"
+
+using namespace zkb;
+
+namespace {
+
+constexpr int NTT_T = 256;     // threads per block
+constexpr int NTT_KMAX = 8;    // butterfly levels per pass
+constexpr int NTT_EMAX = 2048; // elements staged per block (64 KB of shared memory)
+
+__device__ __forceinline__ uint32_t brev(uint32_t x, int bits) { return bits ? (__brev(x) >> (32 - bits)) : 0u; }
+
+__device__ __forceinline__ void smw_put(uint32_t *sm, int E, int idx, const Fr &v)
+{
+#pragma unroll
+    for (int i = 0; i < 8; i++) sm[i * E + idx] = v.v[i];
+}
+__device__ __forceinline__ Fr smw_get(const uint32_t *sm, int E, int idx)
+{
+    Fr v;
+#pragma unroll
+    for (int i = 0; i < 8; i++) v.v[i] = sm[i * E + idx];
+    return v;
+}
+
+// One pass: butterfly levels on index bits [lobits, lobits + k) of every vector, in place.
+// Element index = hi << (lobits + k) | t << lobits | lo; column = hi << lobits | lo.
+// post (optional): result multiplied by post[bitrev_L(index)] on the way out.
+template <bool DIT>
+__global__ void __launch_bounds__(NTT_T)
+k_ntt_pass(Fr *__restrict__ data, size_t vstride, int L, int lobits, int k, int logC, const Fr *__restrict__ tw,
+           const Fr *__restrict__ post)
+{
+    extern __shared__ uint32_t sm[];
+    const int C = 1 << logC, E = C << k;
+    Fr *a = data + (size_t)blockIdx.y * vstride;
+    const uint32_t col0 = blockIdx.x << logC;
+    const uint32_t lomask = (1u << lobits) - 1u;
+    const bool tfast = lobits < logC;
+
+    for (int e = threadIdx.x; e < E; e += NTT_T) {
+        const int col = tfast ? (e >> k) : (e & (C - 1));
+        const int t = tfast ? (e & ((1 << k) - 1)) : (e >> logC);
+        const uint32_t gcol = col0 + col;
+        const size_t idx = ((size_t)(gcol >> lobits) << (lobits + k)) | ((size_t)t << lobits) | (gcol & lomask);
+        smw_put(sm, E, (t << logC) + col, ld_vec(a + idx));
+    }
+    __syncthreads();
+
+    for (int s = 0; s < k; s++) {
+        const int b = DIT ? s : (k - 1 - s);
+        const int sh = L - 1 - lobits - b;
+        for (int j = threadIdx.x; j < (E >> 1); j += NTT_T) {
+            const int col = j & (C - 1);
+            const int tt = j >> logC;
+            const int low = tt & ((1 << b) - 1);
+            const int t0 = ((tt >> b) << (b + 1)) | low;
+            const int i0 = (t0 << logC) + col, i1 = i0 + (1 << (b + logC));
+            const uint32_t lo = (col0 + col) & lomask;
+            const uint32_t ex = (((uint32_t)low << lobits) | lo) << sh;
+            const Fr w = ld_vec_ro(tw + ex);
+            const Fr u = smw_get(sm, E, i0);
+            Fr v = smw_get(sm, E, i1);
+            if (DIT) {
+                v = v * w;
+                smw_put(sm, E, i0, u + v);
+                smw_put(sm, E, i1, u - v);
+            } else {
+                smw_put(sm, E, i0, u + v);
+                smw_put(sm, E, i1, (u - v) * w);
+            }
+        }
+        __syncthreads();
+    }
+
+    for (int e = threadIdx.x; e < E; e += NTT_T) {
+        const int col = tfast ? (e >> k) : (e & (C - 1));
+        const int t = tfast ? (e & ((1 << k) - 1)) : (e >> logC);
+        const uint32_t gcol = col0 + col;
+        const size_t idx = ((size_t)(gcol >> lobits) << (lobits + k)) | ((size_t)t << lobits) | (gcol & lomask);
+        Fr v = smw_get(sm, E, (t << logC) + col);
+        if (post) v = v * ld_vec_ro(post + brev((uint32_t)idx, L));
+        st_vec(a + idx, v);
+    }
+}
+
+// out[bitrev(i)] = in[i]
+__global__ void k_bitrev(const Fr *__restrict__ in, Fr *__restrict__ out, size_t vstride, int L)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >> L) return;
+    const size_t v = blockIdx.y;
+    st_vec(out + v * vstride + brev((uint32_t)i, L), ld_vec(in + v * vstride + i));
+}
+
+// a[i] *= tab[i] (tab may be NULL) * cst (when use_cst)
+__global__ void k_scale(Fr *__restrict__ a, size_t vstride, size_t n, const Fr *__restrict__ tab, Fr cst, int use_cst)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr *p = a + (size_t)blockIdx.y * vstride + i;
+    Fr v = ld_vec(p);
+    if (tab) v = v * ld_vec_ro(tab + i);
+    if (use_cst) v = v * cst;
+    st_vec(p, v);
+}
+
+// out[i] = scale * base^i, i < n
+__global__ void k_powers(Fr *__restrict__ out, size_t n, Fr base, Fr scale)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr acc = scale, b = base;
+    for (size_t e = i; e; e >>= 1) {
+        if (e & 1) acc = acc * b;
+        b = b.sqr();
+    }
+    st_vec(out + i, acc);
+}
+
+// basic domain, last step of the witness map: position p of `a` holds m * g^i * h_i for i = bitrev(p)
+// (unscaled DIF output).  h_i = a[p] * cos_inv[i] -> natural order, Montgomery and plain.
+__global__ void k_h_finish(const Fr *__restrict__ a, size_t vstride, int L, const Fr *__restrict__ cos_inv,
+                           Fr *__restrict__ h_mont, Fr *__restrict__ h_plain, size_t hstride)
+{
+    const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >> L) return;
+    const size_t v = blockIdx.y;
+    const uint32_t i = brev((uint32_t)p, L);
+    const Fr h = ld_vec(a + v * vstride + p) * ld_vec_ro(cos_inv + i);
+    st_vec(h_mont + v * hstride + i, h);
+    if (h_plain) st_vec(h_plain + v * hstride + i, h.from_mont());
+}
+
+// natural-order variant for the step domain: h_i = a[i] * cos_inv[i]
+__global__ void k_h_finish_nat(const Fr *__restrict__ a, size_t vstride, size_t m, const Fr *__restrict__ cos_inv,
+                               Fr *__restrict__ h_mont, Fr *__restrict__ h_plain, size_t hstride)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const size_t v = blockIdx.y;
+    const Fr h = ld_vec(a + v * vstride + i) * ld_vec_ro(cos_inv + i);
+    st_vec(h_mont + v * hstride + i, h);
+    if (h_plain) st_vec(h_plain + v * hstride + i, h.from_mont());
+}
+
+} // namespace
+
+namespace {
+
+// ---- step domain kernels (step_radix2_domain.tcc:39-146) ---------------------------------
+// FFT front end: out = [c (big) | e (small)]
+__global__ void k_step_fft_pre(const Fr *__restrict__ a, Fr *__restrict__ out, size_t vstride, size_t big, size_t small,
+                               const Fr *__restrict__ om_fwd)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= small) return;
+    const Fr *x = a + (size_t)blockIdx.y * vstride;
+    Fr *o = out + (size_t)blockIdx.y * vstride;
+    const Fr lo = ld_vec(x + i), hi = ld_vec(x + big + i);
+    st_vec(o + i, lo + hi);
+    Fr e = (lo - hi) * ld_vec_ro(om_fwd + i);
+    for (size_t k = i + small; k < big; k += small) {
+        const Fr v = ld_vec(x + k);
+        st_vec(o + k, v);
+        e = e + v * ld_vec_ro(om_fwd + k);
+    }
+    st_vec(o + big + i, e);
+}
+
+// iFFT back end: u = [NTT_big^-1 (unscaled) | NTT_small^-1 (unscaled)] -> out = coefficients
+__global__ void k_step_ifft_post(const Fr *__restrict__ u, Fr *__restrict__ out, size_t vstride, size_t big,
+                                 size_t small, const Fr *__restrict__ om_fwd, const Fr *__restrict__ om_inv, Fr big_inv,
+                                 Fr small_inv, Fr half)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= small) return;
+    const Fr *x = u + (size_t)blockIdx.y * vstride;
+    Fr *o = out + (size_t)blockIdx.y * vstride;
+    const Fr u0 = ld_vec(x + i) * big_inv;
+    Fr u1 = ld_vec(x + big + i) * small_inv;
+    for (size_t k = i + small; k < big; k += small) {
+        const Fr v = ld_vec(x + k) * big_inv;
+        st_vec(o + k, v);
+        u1 = u1 - v * ld_vec_ro(om_fwd + k);
+    }
+    u1 = u1 * ld_vec_ro(om_inv + i);
+    st_vec(o + i, (u0 + u1) * half);
+    st_vec(o + big + i, (u0 - u1) * half);
+}
+
+// 1 / Z(g x_i) on the coset (step_radix2_domain.tcc:222-246)
+__global__ void k_step_zinv(Fr *__restrict__ tab, size_t big, size_t small, Fr c0, Fr c1, Fr om2s, Fr z1inv)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= big + small) return;
+    if (i >= big) {
+        st_vec(tab + i, z1inv);
+        return;
+    }
+    Fr elt = Fr::one(), b = om2s;
+    for (size_t e = i; e; e >>= 1) {
+        if (e & 1) elt = elt * b;
+        b = b.sqr();
+    }
+    st_vec(tab + i, (c0 * elt - c1).inverse());
+}
+
+// ---- host-side field helpers (portable path of fp.cuh) -------------------------------------
+Fr fr_from_u64(uint64_t x)
+{
+    Fr r = Fr::zero();
+    r.v[0] = (uint32_t)x;
+    r.v[1] = (uint32_t)(x >> 32);
+    return r.to_mont();
+}
+Fr fr_pow(Fr b, uint64_t e)
+{
+    Fr acc = Fr::one();
+    for (; e; e >>= 1) {
+        if (e & 1) acc = acc * b;
+        b = b.sqr();
+    }
+    return acc;
+}
+// Fr::root_of_unity (alt_bn128_init.cpp:60), Montgomery limbs; order 2^28
+Fr fr_root_of_unity_2_28()
+{
+    static const uint32_t w[8] = {0x80d13d9cu, 0x636e7355u, 0x2445ffd6u, 0xa22bf374u,
+                                  0x1eb203d8u, 0x56452ac0u, 0x2963f9e7u, 0x1860ef94u};
+    Fr r;
+    for (int i = 0; i < 8; i++) r.v[i] = w[i];
+    return r;
+}
+// libff::get_root_of_unity<Fr>(2^logn)  (field_utils.tcc:44-60)
+Fr fr_root_of_unity(int logn)
+{
+    Fr w = fr_root_of_unity_2_28();
+    for (int i = 28; i > logn; i--) w = w.sqr();
+    return w;
+}
+int ceil_log2(size_t n) // libff::log2 (libff/common/utils.cpp)
+{
+    int r = ((n & (n - 1)) == 0 ? 0 : 1);
+    while (n > 1) {
+        n >>= 1;
+        r++;
+    }
+    return r;
+}
+
+int powers(zkb_ctx *ctx, Fr *out, size_t n, const Fr &base, const Fr &scale)
+{
+    if (!n) return ZKB_OK;
+    k_powers<<<ceil_div(n, 128), 128, 0, ctx->stream>>>(out, n, base, scale);
+    ZKB_LAUNCH_CHECK(ctx);
+    return ZKB_OK;
+}
+
+int r2_build(zkb_ctx *ctx, R2Tables *t, int logn, size_t *bytes)
+{
+    t->logn = logn;
+    const size_t half = logn ? ((size_t)1 << (logn - 1)) : 1;
+    ZKB_CUDA(ctx, cudaMalloc(&t->fwd, half * sizeof(Fr)));
+    ZKB_CUDA(ctx, cudaMalloc(&t->inv, half * sizeof(Fr)));
+    *bytes += 2 * half * sizeof(Fr);
+    const Fr w = fr_root_of_unity(logn);
+    int rc = powers(ctx, t->fwd, half, w, Fr::one());
+    if (!rc) rc = powers(ctx, t->inv, half, w.inverse(), Fr::one());
+    return rc;
+}
+
+// all butterfly levels of size 2^T.logn on nvec vectors, in place.
+// dit = false: natural in, bit-reversed out; dit = true: bit-reversed in, natural out.
+int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, size_t vstride, int nvec, const Fr *post)
+{
+    const int L = T.logn;
+    if (L == 0) return ZKB_OK;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(k_ntt_pass<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32);
+        cudaFuncSetAttribute(k_ntt_pass<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32);
+        attr_done = true;
+    }
+    const int P = (L + NTT_KMAX - 1) / NTT_KMAX;
+    int ks[8];
+    for (int p = 0; p < P; p++) ks[p] = L / P + (p < L % P ? 1 : 0);
+    const Fr *tw = inverse ? T.inv : T.fwd;
+    int done = 0;
+    for (int p = 0; p < P; p++) {
+        const int k = ks[p];
+        const int lobits = dit ? done : (L - done - k);
+        int logC = 0;
+        while ((2 << logC << k) <= NTT_EMAX && logC + 1 <= L - k) logC++;
+        const unsigned blocks = 1u << (L - k - logC);
+        const size_t smem = ((size_t)32 << k) << logC;
+        const bool last = p == P - 1;
+        if (dit)
+            k_ntt_pass<true><<<dim3(blocks, nvec), NTT_T, smem, ctx->stream>>>(a, vstride, L, lobits, k, logC, tw, last ? post : nullptr);
+        else
+            k_ntt_pass<false><<<dim3(blocks, nvec), NTT_T, smem, ctx->stream>>>(a, vstride, L, lobits, k, logC, tw, last ? post : nullptr);
+        ZKB_LAUNCH_CHECK(ctx);
+        done += k;
+    }
+    return ZKB_OK;
+}
+
+// natural-order DFT of size 2^T.logn (unscaled), via tmp
+int r2_natural(zkb_ctx *ctx, const R2Tables &T, bool inverse, Fr *a, size_t vstride, int nvec, Fr *tmp)
+{
+    const size_t n = (size_t)1 << T.logn;
+    if (T.logn == 0) return ZKB_OK;
+    int rc = r2_levels(ctx, T, inverse, false, a, vstride, nvec, nullptr);
+    if (rc) return rc;
+    k_bitrev<<<dim3(ceil_div(n, 128), nvec), 128, 0, ctx->stream>>>(a, tmp, vstride, T.logn);
+    ZKB_LAUNCH_CHECK(ctx);
+    ZKB_CUDA(ctx, cudaMemcpy2DAsync(a, vstride * sizeof(Fr), tmp, vstride * sizeof(Fr), n * sizeof(Fr), nvec,
+                                    cudaMemcpyDeviceToDevice, ctx->stream));
+    return ZKB_OK;
+}
+
+int scale(zkb_ctx *ctx, Fr *a, size_t vstride, size_t n, int nvec, const Fr *tab, const Fr *cst)
+{
+    k_scale<<<dim3(ceil_div(n, 128), nvec), 128, 0, ctx->stream>>>(a, vstride, n, tab, cst ? *cst : Fr::one(), cst ? 1 : 0);
+    ZKB_LAUNCH_CHECK(ctx);
+    return ZKB_OK;
+}
+
+} // namespace
+
+namespace zkb {
+
+int domain_select_host(size_t min_size, size_t *m_out, int *kind_out)
+{
+    if (min_size <= 1) return ZKB_ERR_DOMAIN;
+    auto is_pow2 = [](size_t x) { return x && !(x & (x - 1)); };
+    auto basic_ok = [&](size_t m) { return m > 1 && is_pow2(m) && ceil_log2(m) <= 28; };
+    auto step_ok = [&](size_t m) {
+        if (m <= 1) return false;
+        const int lg = ceil_log2(m);
+        const size_t big = (size_t)1 << (lg - 1), small = m - big;
+        return is_pow2(small) && lg <= 28;
+    };
+    const size_t big = (size_t)1 << (ceil_log2(min_size) - 1);
+    const size_t small = min_size - big;
+    const size_t rounded_small = (size_t)1 << ceil_log2(small);
+    // order of get_evaluation_domain.tcc:41-49; extended_radix2 (log m == 29) and the geometric / arithmetic
+    // sequence domains are not supported: sizes that would reach them report ZKB_ERR_DOMAIN
+    const size_t cand[2] = {min_size, big + rounded_small};
+    for (int t = 0; t < 2; t++) {
+        if (basic_ok(cand[t])) {
+            *m_out = cand[t];
+            *kind_out = ZKB_DOMAIN_BASIC_RADIX2;
+            return ZKB_OK;
+        }
+        if (ceil_log2(cand[t]) == 29) return ZKB_ERR_DOMAIN;
+        if (step_ok(cand[t])) {
+            *m_out = cand[t];
+            *kind_out = ZKB_DOMAIN_STEP_RADIX2;
+            return ZKB_OK;
+        }
+    }
+    return ZKB_ERR_DOMAIN;
+}
+
+void domain_free(Domain *d)
+{
+    Fr *ptrs[] = {d->big.fwd, d->big.inv, d->small.fwd, d->small.inv, d->cos_fwd, d->cos_inv, d->zinv_tab, d->om_fwd, d->om_inv};
+    for (Fr *p : ptrs)
+        if (p) cudaFree(p);
+    *d = Domain();
+}
+
+int domain_build(zkb_ctx *ctx, size_t m, int kind, Domain *d)
+{
+    *d = Domain();
+    d->kind = kind;
+    d->dev = ctx->dev;
+    d->m = m;
+    const Fr g = fr_from_u64(5); // Fr::multiplicative_generator (alt_bn128_init.cpp:59)
+    const Fr ginv = g.inverse();
+    int rc;
+    ZKB_CUDA(ctx, cudaMalloc(&d->cos_fwd, m * sizeof(Fr)));
+    ZKB_CUDA(ctx, cudaMalloc(&d->cos_inv, m * sizeof(Fr)));
+    d->bytes += 2 * m * sizeof(Fr);
+    if (kind == ZKB_DOMAIN_BASIC_RADIX2) {
+        d->big_m = m;
+        if ((rc = r2_build(ctx, &d->big, ceil_log2(m), &d->bytes))) return rc;
+        const Fr minv = fr_from_u64(m).inverse();
+        if ((rc = powers(ctx, d->cos_fwd, m, g, minv))) return rc;
+        if ((rc = powers(ctx, d->cos_inv, m, ginv, minv))) return rc;
+        d->zinv = (fr_pow(g, m) - Fr::one()).inverse();
+    } else if (kind == ZKB_DOMAIN_STEP_RADIX2) {
+        const int lg = ceil_log2(m);
+        d->big_m = (size_t)1 << (lg - 1);
+        d->small_m = m - d->big_m;
+        if ((rc = r2_build(ctx, &d->big, lg - 1, &d->bytes))) return rc;
+        if ((rc = r2_build(ctx, &d->small, ceil_log2(d->small_m), &d->bytes))) return rc;
+        if ((rc = powers(ctx, d->cos_fwd, m, g, Fr::one()))) return rc;
+        if ((rc = powers(ctx, d->cos_inv, m, ginv, Fr::one()))) return rc;
+        const Fr omega = fr_root_of_unity(lg);
+        ZKB_CUDA(ctx, cudaMalloc(&d->om_fwd, d->big_m * sizeof(Fr)));
+        ZKB_CUDA(ctx, cudaMalloc(&d->om_inv, d->small_m * sizeof(Fr)));
+        ZKB_CUDA(ctx, cudaMalloc(&d->zinv_tab, m * sizeof(Fr)));
+        d->bytes += (d->big_m + d->small_m + m) * sizeof(Fr);
+        if ((rc = powers(ctx, d->om_fwd, d->big_m, omega, Fr::one()))) return rc;
+        if ((rc = powers(ctx, d->om_inv, d->small_m, omega.inverse(), Fr::one()))) return rc;
+        // step_radix2_domain.tcc:222-246
+        const Fr Z0 = fr_pow(g, d->big_m) - Fr::one();
+        const Fr c0 = fr_pow(g, d->small_m) * Z0;
+        const Fr c1 = fr_pow(omega, d->small_m) * Z0;
+        const Fr om2s = fr_pow(omega, 2 * d->small_m);
+        const Fr go = g * omega;
+        const Fr Z1 = (fr_pow(go, d->big_m) - Fr::one()) * (fr_pow(go, d->small_m) - fr_pow(omega, d->small_m));
+        k_step_zinv<<<ceil_div(m, 128), 128, 0, ctx->stream>>>(d->zinv_tab, d->big_m, d->small_m, c0, c1, om2s, Z1.inverse());
+        ZKB_LAUNCH_CHECK(ctx);
+    } else {
+        return fail(ctx, ZKB_ERR_DOMAIN, "unsupported evaluation domain kind");
+    }
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ZKB_OK;
+}
+
+// ---- step domain, natural order (step_radix2_domain.tcc:39-146) ------------------------------
+static int step_fft(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp)
+{
+    k_step_fft_pre<<<dim3(ceil_div(d->small_m, 128), nvec), 128, 0, ctx->stream>>>(a, tmp, vstride, d->big_m, d->small_m, d->om_fwd);
+    ZKB_LAUNCH_CHECK(ctx);
+    int rc = r2_natural(ctx, d->big, false, tmp, vstride, nvec, a);
+    if (!rc) rc = r2_natural(ctx, d->small, false, tmp + d->big_m, vstride, nvec, a + d->big_m);
+    if (rc) return rc;
+    ZKB_CUDA(ctx, cudaMemcpy2DAsync(a, vstride * sizeof(Fr), tmp, vstride * sizeof(Fr), d->m * sizeof(Fr), nvec,
+                                    cudaMemcpyDeviceToDevice, ctx->stream));
+    return ZKB_OK;
+}
+
+static int step_ifft(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp)
+{
+    int rc = r2_natural(ctx, d->big, true, a, vstride, nvec, tmp);
+    if (!rc) rc = r2_natural(ctx, d->small, true, a + d->big_m, vstride, nvec, tmp + d->big_m);
+    if (rc) return rc;
+    const Fr big_inv = fr_from_u64(d->big_m).inverse(), small_inv = fr_from_u64(d->small_m).inverse();
+    const Fr half = fr_from_u64(2).inverse();
+    k_step_ifft_post<<<dim3(ceil_div(d->small_m, 128), nvec), 128, 0, ctx->stream>>>(a, tmp, vstride, d->big_m, d->small_m, d->om_fwd,
+                                                                                   d->om_inv, big_inv, small_inv, half);
+    ZKB_LAUNCH_CHECK(ctx);
+    ZKB_CUDA(ctx, cudaMemcpy2DAsync(a, vstride * sizeof(Fr), tmp, vstride * sizeof(Fr), d->m * sizeof(Fr), nvec,
+                                    cudaMemcpyDeviceToDevice, ctx->stream));
+    return ZKB_OK;
+}
+
+int domain_op(zkb_ctx *ctx, const Domain *d, int op, Fr *a, size_t vstride, int nvec, Fr *tmp)
+{
+    const bool basic = d->kind == ZKB_DOMAIN_BASIC_RADIX2;
+    const Fr m_scal = fr_from_u64(d->m);       // undoes the 1/m folded into the basic coset tables
+    const Fr minv = m_scal.inverse();
+    int rc = ZKB_OK;
+    switch (op) {
+    case ZKB_NTT_COSET_FFT:
+        if ((rc = scale(ctx, a, vstride, d->m, nvec, d->cos_fwd, basic ? &m_scal : nullptr))) return rc;
+        /* fall through */
+    case ZKB_NTT_FFT:
+        return basic ? r2_natural(ctx, d->big, false, a, vstride, nvec, tmp) : step_fft(ctx, d, a, vstride, nvec, tmp);
+    case ZKB_NTT_IFFT:
+    case ZKB_NTT_ICOSET_FFT:
+        if (basic) {
+            if ((rc = r2_natural(ctx, d->big, true, a, vstride, nvec, tmp))) return rc;
+            // 1/m, and g^-i for the coset variant (cos_inv already carries the 1/m)
+            return op == ZKB_NTT_IFFT ? scale(ctx, a, vstride, d->m, nvec, nullptr, &minv)
+                                      : scale(ctx, a, vstride, d->m, nvec, d->cos_inv, nullptr);
+        }
+        if ((rc = step_ifft(ctx, d, a, vstride, nvec, tmp))) return rc;
+        return op == ZKB_NTT_IFFT ? ZKB_OK : scale(ctx, a, vstride, d->m, nvec, d->cos_inv, nullptr);
+    case ZKB_NTT_DIV_Z_ON_COSET:
+        return basic ? scale(ctx, a, vstride, d->m, nvec, nullptr, &d->zinv) : scale(ctx, a, vstride, d->m, nvec, d->zinv_tab, nullptr);
+    default:
+        return fail(ctx, ZKB_ERR_ARG, "zkb_domain_op: unknown operation");
+    }
+}
+
+int domain_to_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp)
+{
+    if (d->kind == ZKB_DOMAIN_BASIC_RADIX2) {
+        // DIF inverse (bit-reversed out), times g^i / m in bit-reversed order, DIT forward (natural out)
+        int rc = r2_levels(ctx, d->big, true, false, a, vstride, nvec, d->cos_fwd);
+        if (!rc) rc = r2_levels(ctx, d->big, false, true, a, vstride, nvec, nullptr);
+        return rc;
+    }
+    int rc = step_ifft(ctx, d, a, vstride, nvec, tmp);
+    if (!rc) rc = scale(ctx, a, vstride, d->m, nvec, d->cos_fwd, nullptr);
+    if (!rc) rc = step_fft(ctx, d, a, vstride, nvec, tmp);
+    return rc;
+}
+
+int domain_h_from_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp, Fr *h_mont, Fr *h_plain,
+                        size_t hstride)
+{
+    const dim3 grid(ceil_div(d->m, 128), nvec);
+    if (d->kind == ZKB_DOMAIN_BASIC_RADIX2) {
+        // the constant 1 / Z(g) commutes with the transform: folded into the caller's pointwise pass
+        int rc = r2_levels(ctx, d->big, true, false, a, vstride, nvec, nullptr);
+        if (rc) return rc;
+        k_h_finish<<<grid, 128, 0, ctx->stream>>>(a, vstride, d->big.logn, d->cos_inv, h_mont, h_plain, hstride);
+        ZKB_LAUNCH_CHECK(ctx);
+        return ZKB_OK;
+    }
+    int rc = scale(ctx, a, vstride, d->m, nvec, d->zinv_tab, nullptr);
+    if (!rc) rc = step_ifft(ctx, d, a, vstride, nvec, tmp);
+    if (rc) return rc;
+    k_h_finish_nat<<<grid, 128, 0, ctx->stream>>>(a, vstride, d->m, d->cos_inv, h_mont, h_plain, hstride);
+    ZKB_LAUNCH_CHECK(ctx);
+    return ZKB_OK;
+}
+
+} // namespace zkb
+
+extern "C" {
+
+int zkb_domain_select(size_t min_size, size_t *m_out, int *kind_out)
+{
+    if (!m_out || !kind_out) return ZKB_ERR_ARG;
+    return domain_select_host(min_size, m_out, kind_out);
+}
+
+int zkb_domain_op(zkb_ctx *ctx, size_t min_size, int op, uint64_t *data)
+{
+    if (!ctx || !data) return fail(ctx, ZKB_ERR_ARG, "zkb_domain_op: bad argument");
+    size_t m;
+    int kind;
+    if (domain_select_host(min_size, &m, &kind)) return fail(ctx, ZKB_ERR_DOMAIN, "zkb_domain_op: no supported evaluation domain");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    Domain d;
+    int rc = domain_build(ctx, m, kind, &d);
+    if (!rc) {
+        rc = ZKB_ERR_CUDA;
+        if (ctx->scratch[SB_STAGE_A].ensure(m * sizeof(Fr)) == cudaSuccess && ctx->scratch[SB_STAGE_B].ensure(m * sizeof(Fr)) == cudaSuccess) {
+            Fr *a = ctx->scratch[SB_STAGE_A].as<Fr>(), *tmp = ctx->scratch[SB_STAGE_B].as<Fr>();
+            cudaMemcpyAsync(a, data, m * sizeof(Fr), cudaMemcpyHostToDevice, ctx->stream);
+            cudaEventRecord(ctx->ev0, ctx->stream);
+            rc = domain_op(ctx, &d, op, a, m, 1, tmp);
+            cudaEventRecord(ctx->ev1, ctx->stream);
+            if (!rc) {
+                cudaMemcpyAsync(data, a, m * sizeof(Fr), cudaMemcpyDeviceToHost, ctx->stream);
+                if (cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+                    rc = fail(ctx, ZKB_ERR_CUDA, std::string("zkb_domain_op: ") + cudaGetErrorString(cudaGetLastError()));
+                float ms = 0;
+                cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+                ctx->last_ms = ms;
+            }
+        } else
+            fail(ctx, ZKB_ERR_CUDA, "zkb_domain_op: out of device memory");
+    }
+    domain_free(&d);
+    return rc;
+}
+
+} // extern "C"

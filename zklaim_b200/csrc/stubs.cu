@@ -2,8 +2,6 @@
 #include "common.cuh"
 using namespace zkb;
 extern "C" {
-int zkb_domain_select(size_t, size_t *, int *) { return ZKB_ERR_DOMAIN; }
-int zkb_domain_op(zkb_ctx *ctx, size_t, int, uint64_t *) { return fail(ctx, ZKB_ERR_ARG, "not implemented"); }
 int zkb_key_upload(zkb_ctx *ctx, const zkb_key_desc *, zkb_key **) { return fail(ctx, ZKB_ERR_ARG, "not implemented"); }
 void zkb_key_free(zkb_key *) {}
 size_t zkb_key_device_bytes(const zkb_key *) { return 0; }
