@@ -172,6 +172,11 @@ int zkb_prove(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_
 int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r,
                     const uint64_t *s, zkb_proof *out);
 
+/* Same with w (count x num_variables x 4 limbs), r and s (count x 4 limbs) already in device memory
+ * on the context's device; the proofs still come back to the host (384 bytes each). */
+int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const void *d_w, const void *d_r,
+                           const void *d_s, zkb_proof *out);
+
 /* ---- measurement helpers (used by bench.py only) ------------------------------------ */
 /* Sustained integer multiply-add rate of the device: independent mad.wide.u32 chains on all
  * SMs; returns 32x32+64->64 multiply-adds per second, or < 0 on error. */

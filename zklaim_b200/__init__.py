@@ -57,6 +57,7 @@ SYMBOLS = {
     "zkb_witness_map": (_i, [_vp, _vp, _u64p, _u64p]),
     "zkb_prove": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _vp, _u64p]),
     "zkb_prove_batch": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p, _vp]),
+    "zkb_prove_batch_device": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
     "zkb_measure_imad_peak": (C.c_double, [_vp, _i]),
     "zkb_last_device_ms": (C.c_double, [_vp]),
     "zkb_last_kernel_launches": (C.c_long, [_vp]),
@@ -263,6 +264,12 @@ class Context:
         assert w.shape[0] == count and s.shape[0] == count
         out = (Proof * count)()
         self._chk(self.lib.zkb_prove_batch(self.h, key.h, count, w.ctypes.data, r.ctypes.data, s.ctypes.data, out))
+        return np.stack([p.as_array() for p in out])
+
+    def prove_batch_device(self, key: "Key", d_w: int, d_r: int, d_s: int, count: int) -> np.ndarray:
+        """w, r, s are CUDA device pointers (e.g. torch tensors' data_ptr()) on this context's device."""
+        out = (Proof * count)()
+        self._chk(self.lib.zkb_prove_batch_device(self.h, key.h, count, d_w, d_r, d_s, out))
         return np.stack([p.as_array() for p in out])
 
     # ---- measurement ------------------------------------------------------------------

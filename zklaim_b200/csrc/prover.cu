@@ -1,0 +1,509 @@
+// prover.cu -- the Groth16 prover of libsnark's r1cs_gg_ppzksnark on one B200, batched over proofs.
+//
+// Replaces r1cs_gg_ppzksnark_prover (libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/
+// r1cs_gg_ppzksnark.tcc:390-505) and r1cs_to_qap_witness_map with d1 = d2 = d3 = 0
+// (libsnark/reductions/r1cs_to_qap/r1cs_to_qap.tcc:205-334).  A proving key is uploaded once
+// (zkb_key_upload); every later call works on a batch of witnesses with one launch per stage
+// for the whole batch:
+//
+//   Z (one row per proof) = [ 1 | w (nv) | r | s | -rs | H coefficients (m + 1) ]   Montgomery Fr
+//   P = the same row as plain integers (MSM digits are cut from it)
+//
+//   1. sparse matrix-vector products  aA = A z, aB = B z, aC = C z  (z = [1 | w], CSR rows =
+//      constraints, r1cs_to_qap.tcc:228-238, :277-283) plus the satisfiability check;
+//   2. iFFT + cosetFFT of the 3 * batch vectors (ntt.cu), H = (A B - C) / Z on the coset,
+//      icosetFFT -> H coefficients written straight into Z and P;
+//   3. one G1 MSM run with three jobs and one G2 run with one job (msm.cu).  The fixed key
+//      elements ride along as extra bases so that no variable-time work is left for them:
+//        job A  = A_query + {alpha_g1 (scalar 1), delta_g1 (scalar r)}      = g1_A  (tcc:488)
+//        job B1 = B_query.h + {beta_g1 (1), delta_g1 (s)}                     = g1_B  (tcc:491)
+//        job C  = H_query + L_query + {delta_g1 (-rs)}                        = Ht + Lt - rs delta
+//        job B2 = B_query.g + {beta_g2 (1), delta_g2 (s)}                     = g2_B  (tcc:492)
+//   4. assembly: g1_C = job C + s g1_A + r g1_B  (tcc:495), two scalar multiplications per proof.
+#define ZKB_NOINLINE_MUL 1
+#include "msm_impl.cuh"
+#include "ntt.cuh"
+#include <string.h>
+
+using namespace zkb;
+
+struct zkb_key {
+    int dev = 0;
+    size_t nc = 0, nv = 0, ni = 0, m = 0;
+    int kind = 0;
+    Domain dom;
+    uint32_t *rowptr[3] = {nullptr, nullptr, nullptr};
+    uint32_t *col[3] = {nullptr, nullptr, nullptr};
+    Fr *coeff[3] = {nullptr, nullptr, nullptr};
+    size_t nnz[3] = {0, 0, 0};
+    MsmPlan g1, g2;
+    size_t zlen = 0; // elements per row of Z
+    size_t bytes = 0;
+    // offsets into a row of Z
+    size_t z_w() const { return 1; }
+    size_t z_r() const { return nv + 1; }
+    size_t z_s() const { return nv + 2; }
+    size_t z_nrs() const { return nv + 3; }
+    size_t z_h() const { return nv + 4; }
+};
+
+namespace {
+
+enum { SP_Z = SB_PROVER0, SP_P, SP_ABC, SP_TMP, SP_RS, SP_FLAGS, SP_PROOF, SP_W, SP_RES1, SP_RES2 };
+
+struct CsrDev {
+    const uint32_t *rowptr[3];
+    const uint32_t *col[3];
+    const Fr *coeff[3];
+};
+
+__device__ __forceinline__ bool is_mont_one(const Fr &a)
+{
+    uint32_t o = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) o |= a.v[i] ^ FrP::ONE(i);
+    return o == 0;
+}
+
+// abc[(mat * batch + p) * m + row] = <row of matrix mat, z_p>; rows >= nc: the input-consistency
+// constraints of r1cs_to_qap.tcc:228-231 for A, zero for B and C.
+__global__ void __launch_bounds__(128)
+k_spmv(CsrDev csr, const Fr *__restrict__ Z, size_t zlen, size_t nc, size_t ni, size_t m, int batch, Fr *__restrict__ abc)
+{
+    const size_t row = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= m) return;
+    const int mat = blockIdx.y, p = blockIdx.z;
+    const Fr *z = Z + (size_t)p * zlen;
+    Fr acc = Fr::zero();
+    if (row < nc) {
+        const uint32_t lo = csr.rowptr[mat][row], hi = csr.rowptr[mat][row + 1];
+        for (uint32_t e = lo; e < hi; e++) {
+            const Fr c = ld_vec_ro(csr.coeff[mat] + e);
+            const Fr x = ld_vec(z + csr.col[mat][e]);
+            acc = acc + (is_mont_one(c) ? x : c * x);
+        }
+    } else if (mat == 0 && row - nc <= ni) {
+        acc = ld_vec(z + (row - nc));
+    }
+    st_vec(abc + ((size_t)mat * batch + p) * m + row, acc);
+}
+
+// r1cs_constraint_system::is_satisfied (r1cs.tcc): <a,z> * <b,z> == <c,z> for every constraint
+__global__ void k_sat_check(const Fr *__restrict__ abc, size_t nc, size_t m, int batch, uint32_t *__restrict__ flags)
+{
+    const size_t row = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nc) return;
+    const int p = blockIdx.y;
+    const Fr a = ld_vec(abc + ((size_t)0 * batch + p) * m + row);
+    const Fr b = ld_vec(abc + ((size_t)1 * batch + p) * m + row);
+    const Fr c = ld_vec(abc + ((size_t)2 * batch + p) * m + row);
+    if (a * b != c) atomicOr(flags + p, 1u);
+}
+
+// A <- (A * B - C) [* zinv]   on the coset (r1cs_to_qap.tcc:270-303)
+__global__ void k_h_pointwise(Fr *__restrict__ abc, size_t m, int batch, Fr zinv, int use_zinv)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const int p = blockIdx.y;
+    Fr *a = abc + ((size_t)0 * batch + p) * m + i;
+    const Fr b = ld_vec(abc + ((size_t)1 * batch + p) * m + i);
+    const Fr c = ld_vec(abc + ((size_t)2 * batch + p) * m + i);
+    Fr h = ld_vec(a) * b - c;
+    if (use_zinv) h = h * zinv;
+    st_vec(a, h);
+}
+
+// fixed entries of a row of Z: 1, r, s, -rs, and the top coefficient H[m] = 0 (d1 = d2 = d3 = 0)
+__global__ void k_z_fill(Fr *__restrict__ Z, size_t zlen, size_t nv, size_t m, const Fr *__restrict__ rs, int batch)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= batch) return;
+    Fr *z = Z + (size_t)p * zlen;
+    const Fr r = ld_vec(rs + 2 * p), s = ld_vec(rs + 2 * p + 1);
+    st_vec(z, Fr::one());
+    st_vec(z + nv + 1, r);
+    st_vec(z + nv + 2, s);
+    st_vec(z + nv + 3, (r * s).neg());
+    st_vec(z + nv + 4 + m, Fr::zero());
+}
+
+// P[0 .. n) = plain form of Z[0 .. n) for every proof
+__global__ void k_z_plain(const Fr *__restrict__ Z, Fr *__restrict__ P, size_t zlen, size_t n)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const size_t o = (size_t)blockIdx.y * zlen + i;
+    st_vec(P + o, ld_vec(Z + o).from_mont());
+}
+
+// g1_C = job C + s * g1_A + r * g1_B (r1cs_gg_ppzksnark.tcc:495); proof = (g1_A, g2_B, g1_C) as Jacobian limbs
+__global__ void __launch_bounds__(64)
+k_assemble(const G1X *__restrict__ r1, const G2X *__restrict__ r2, const Fr *__restrict__ P, size_t zlen, size_t nv,
+           zkb_proof *__restrict__ out)
+{
+    __shared__ G1X sh[2];
+    const int p = blockIdx.x;
+    const Fr *pl = P + (size_t)p * zlen;
+    const int t = threadIdx.x;
+    if (t == 0 || t == 32) {
+        const int which = t >> 5; // 0: s * g1_A, 1: r * g1_B
+        const Fr k = ld_vec(pl + (which == 0 ? nv + 2 : nv + 1));
+        sh[which] = scalar_mul<Fq>(k.v, ld_vec(r1 + 3 * (size_t)p + which));
+    }
+    __syncthreads();
+    if (t == 0) {
+        G1X c = ld_vec(r1 + 3 * (size_t)p + 2);
+        c.add(sh[0]);
+        c.add(sh[1]);
+        const G1J A = ld_vec(r1 + 3 * (size_t)p).to_jacobian(), C = c.to_jacobian();
+        st_vec(reinterpret_cast<G1J *>(out[p].A), A);
+        st_vec(reinterpret_cast<G1J *>(out[p].C), C);
+    }
+    if (t == 32) st_vec(reinterpret_cast<G2J *>(out[p].B), ld_vec(r2 + p).to_jacobian());
+}
+
+} // namespace
+
+namespace {
+
+int upload_csr(zkb_ctx *ctx, zkb_key *key, int mat, const zkb_csr &h)
+{
+    const size_t nc = key->nc;
+    if (!h.row_ptr || (h.row_ptr[nc] && (!h.col || !h.coeff))) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: CSR pointers missing");
+    const size_t nnz = h.row_ptr[nc];
+    if (nnz >= (1ull << 32)) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: more than 2^32 matrix entries");
+    std::vector<uint32_t> rp(nc + 1);
+    for (size_t i = 0; i <= nc; i++) {
+        if (h.row_ptr[i] > nnz || (i && h.row_ptr[i] < h.row_ptr[i - 1])) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: CSR row_ptr not monotone");
+        rp[i] = (uint32_t)h.row_ptr[i];
+    }
+    for (size_t e = 0; e < nnz; e++)
+        if (h.col[e] > key->nv) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: CSR column out of range");
+    key->nnz[mat] = nnz;
+    ZKB_CUDA(ctx, cudaMalloc(&key->rowptr[mat], (nc + 1) * 4));
+    ZKB_CUDA(ctx, cudaMalloc(&key->col[mat], (nnz + 1) * 4));
+    ZKB_CUDA(ctx, cudaMalloc(&key->coeff[mat], (nnz + 1) * sizeof(Fr)));
+    key->bytes += (nc + 1) * 4 + (nnz + 1) * 36;
+    ZKB_CUDA(ctx, cudaMemcpy(key->rowptr[mat], rp.data(), (nc + 1) * 4, cudaMemcpyHostToDevice));
+    if (nnz) {
+        ZKB_CUDA(ctx, cudaMemcpy(key->col[mat], h.col, nnz * 4, cudaMemcpyHostToDevice));
+        ZKB_CUDA(ctx, cudaMemcpy(key->coeff[mat], h.coeff, nnz * sizeof(Fr), cudaMemcpyHostToDevice));
+    }
+    return ZKB_OK;
+}
+
+// appends `n` points of `words` u64 each to a host staging vector
+void append_pts(std::vector<uint64_t> &v, const uint64_t *src, size_t n, int words) { v.insert(v.end(), src, src + n * words); }
+
+void key_release(zkb_key *key)
+{
+    if (!key) return;
+    cudaSetDevice(key->dev);
+    for (int k = 0; k < 3; k++) {
+        if (key->rowptr[k]) cudaFree(key->rowptr[k]);
+        if (key->col[k]) cudaFree(key->col[k]);
+        if (key->coeff[k]) cudaFree(key->coeff[k]);
+    }
+    plan_free(&key->g1);
+    plan_free(&key->g2);
+    domain_free(&key->dom);
+    delete key;
+}
+
+int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key)
+{
+    key->dev = ctx->dev;
+    key->nc = d->num_constraints;
+    key->nv = d->num_variables;
+    key->ni = d->num_inputs;
+    const size_t nv = key->nv, ni = key->ni;
+    if (ni > nv) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: num_inputs > num_variables");
+    // r1cs_to_qap.tcc:218: domain for num_constraints + num_inputs + 1 points
+    if (domain_select_host(key->nc + ni + 1, &key->m, &key->kind))
+        return fail(ctx, ZKB_ERR_DOMAIN, "zkb_key_upload: no supported evaluation domain for this constraint system");
+    const size_t m = key->m;
+    if (d->H_size != m - 1) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: H_query size must be domain size - 1");
+    if (nv + m + 8 >= (1ull << 31)) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: key too large");
+    for (size_t k = 0; k < d->B_nnz; k++)
+        if (d->B_index[k] > nv) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: B_query index out of range");
+    int rc;
+    if ((rc = domain_build(ctx, m, key->kind, &key->dom))) return rc;
+    key->bytes += key->dom.bytes;
+    const zkb_csr *mats[3] = {&d->A, &d->B, &d->C};
+    for (int k = 0; k < 3; k++)
+        if ((rc = upload_csr(ctx, key, k, *mats[k]))) return rc;
+    key->zlen = (nv + 4 + m + 1 + 3) & ~(size_t)3;
+
+    // ---- G1 plan: jobs A, B1, C ----
+    const size_t nA = nv + 3, nB = d->B_nnz + 2, nL = nv - ni, nC = (m - 1) + nL + 1;
+    key->g1.group = ZKB_G1;
+    key->g2.group = ZKB_G2;
+    // witness-driven queries are mostly 0 / 1 scalars in practice (r1cs_gg_ppzksnark.tcc:442-485 uses the
+    // mixed-addition variants for them); H is dense
+    if ((rc = plan_add_job(ctx, &key->g1, nA, msm_choose_c(nA / 4 + 1, ZKB_G1, 0), 0))) return rc;
+    if ((rc = plan_add_job(ctx, &key->g1, nB, msm_choose_c(nB / 4 + 1, ZKB_G1, 0), 0))) return rc;
+    if ((rc = plan_add_job(ctx, &key->g1, nC, msm_choose_c((m - 1) + nL / 4 + 1, ZKB_G1, 0), 0))) return rc;
+    if ((rc = plan_add_job(ctx, &key->g2, nB, msm_choose_c(nB / 4 + 1, ZKB_G2, 0), 0))) return rc;
+    if ((rc = plan_alloc(ctx, &key->g1))) return rc;
+    if ((rc = plan_alloc(ctx, &key->g2))) return rc;
+    key->bytes += key->g1.bytes + key->g2.bytes;
+
+    std::vector<uint64_t> st;
+    std::vector<uint32_t> sidx1, sidx2;
+    sidx1.reserve(nA + nB + nC);
+    // job A
+    st.reserve(nC * 8);
+    append_pts(st, d->A_query, nv + 1, 8);
+    append_pts(st, d->alpha_g1, 1, 8);
+    append_pts(st, d->delta_g1, 1, 8);
+    for (size_t i = 0; i <= nv; i++) sidx1.push_back((uint32_t)i);
+    sidx1.push_back(0);
+    sidx1.push_back((uint32_t)key->z_r());
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1, 0, st.data()))) return rc;
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    // job B1
+    st.clear();
+    append_pts(st, d->B_g1, d->B_nnz, 8);
+    append_pts(st, d->beta_g1, 1, 8);
+    append_pts(st, d->delta_g1, 1, 8);
+    for (size_t k = 0; k < d->B_nnz; k++) sidx1.push_back(d->B_index[k]);
+    sidx1.push_back(0);
+    sidx1.push_back((uint32_t)key->z_s());
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1, 1, st.data()))) return rc;
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    // job C
+    st.clear();
+    append_pts(st, d->H_query, m - 1, 8);
+    append_pts(st, d->L_query, nL, 8);
+    append_pts(st, d->delta_g1, 1, 8);
+    for (size_t j = 0; j + 1 < m; j++) sidx1.push_back((uint32_t)(key->z_h() + j));
+    for (size_t j = 0; j < nL; j++) sidx1.push_back((uint32_t)(1 + ni + j));
+    sidx1.push_back((uint32_t)key->z_nrs());
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1, 2, st.data()))) return rc;
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    // job B2
+    st.clear();
+    append_pts(st, d->B_g2, d->B_nnz, 16);
+    append_pts(st, d->beta_g2, 1, 16);
+    append_pts(st, d->delta_g2, 1, 16);
+    for (size_t k = 0; k < d->B_nnz; k++) sidx2.push_back(d->B_index[k]);
+    sidx2.push_back(0);
+    sidx2.push_back((uint32_t)key->z_s());
+    if ((rc = plan_upload_job<Fq2>(ctx, &key->g2, 0, st.data()))) return rc;
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+
+    ZKB_CUDA(ctx, cudaMalloc(&key->g1.d_sidx, sidx1.size() * 4));
+    ZKB_CUDA(ctx, cudaMalloc(&key->g2.d_sidx, sidx2.size() * 4));
+    ZKB_CUDA(ctx, cudaMemcpy(key->g1.d_sidx, sidx1.data(), sidx1.size() * 4, cudaMemcpyHostToDevice));
+    ZKB_CUDA(ctx, cudaMemcpy(key->g2.d_sidx, sidx2.size() ? sidx2.data() : nullptr, sidx2.size() * 4, cudaMemcpyHostToDevice));
+    key->bytes += (sidx1.size() + sidx2.size()) * 4;
+    return ZKB_OK;
+}
+
+size_t pairs_per_proof(const MsmPlan &pl)
+{
+    size_t e = 0;
+    for (uint32_t q = 0; q < pl.tab.njobs; q++) e += (size_t)pl.tab.j[q].n * pl.tab.j[q].W;
+    return e;
+}
+
+// proofs per chunk: bounded by the 2^32 pair-list positions of one MSM run and a scratch-memory budget
+int chunk_size(const zkb_key *key, size_t count)
+{
+    const size_t e1 = pairs_per_proof(key->g1), e2 = pairs_per_proof(key->g2);
+    const size_t per_proof = e1 * 8 + e1 / 4 * 16 + (size_t)key->g1.tab.Bp * 132 + e2 * 8 + e2 / 4 * 32 +
+                             (size_t)key->g2.tab.Bp * 260 + key->m * 32 * 6 + key->zlen * 64;
+    size_t c = 64;
+    const size_t budget = (size_t)32 << 30;
+    if (c > budget / per_proof) c = budget / per_proof;
+    if (c > ((1ull << 31) / (e1 + 1))) c = (1ull << 31) / (e1 + 1);
+    if (c > ((1ull << 31) / ((size_t)key->g1.tab.Bp + 1))) c = (1ull << 31) / ((size_t)key->g1.tab.Bp + 1);
+    if (c > count) c = count;
+    return c ? (int)c : 1;
+}
+
+// Z rows for `batch` proofs are in place (w, r, s uploaded); runs stages 1-2.  Leaves H in Z and P.
+int witness_map_chunk(zkb_ctx *ctx, const zkb_key *key, int batch, uint32_t *d_flags)
+{
+    cudaStream_t st = ctx->stream;
+    const size_t m = key->m;
+    Fr *Z = ctx->scratch[SP_Z].as<Fr>(), *P = ctx->scratch[SP_P].as<Fr>();
+    ZKB_CUDA(ctx, ctx->scratch[SP_ABC].ensure((size_t)3 * batch * m * sizeof(Fr)));
+    Fr *abc = ctx->scratch[SP_ABC].as<Fr>();
+    Fr *tmp = nullptr;
+    if (key->kind != ZKB_DOMAIN_BASIC_RADIX2) {
+        ZKB_CUDA(ctx, ctx->scratch[SP_TMP].ensure((size_t)3 * batch * m * sizeof(Fr)));
+        tmp = ctx->scratch[SP_TMP].as<Fr>();
+    }
+    CsrDev csr;
+    for (int k = 0; k < 3; k++) {
+        csr.rowptr[k] = key->rowptr[k];
+        csr.col[k] = key->col[k];
+        csr.coeff[k] = key->coeff[k];
+    }
+    k_spmv<<<dim3(ceil_div(m, 128), 3, batch), 128, 0, st>>>(csr, Z, key->zlen, key->nc, key->ni, m, batch, abc);
+    ZKB_LAUNCH_CHECK(ctx);
+    if (key->nc) {
+        k_sat_check<<<dim3(ceil_div(key->nc, 128), batch), 128, 0, st>>>(abc, key->nc, m, batch, d_flags);
+        ZKB_LAUNCH_CHECK(ctx);
+    }
+    int rc = domain_to_coset(ctx, &key->dom, abc, m, 3 * batch, tmp);
+    if (rc) return rc;
+    const bool basic = key->kind == ZKB_DOMAIN_BASIC_RADIX2;
+    k_h_pointwise<<<dim3(ceil_div(m, 128), batch), 128, 0, st>>>(abc, m, batch, key->dom.zinv, basic ? 1 : 0);
+    ZKB_LAUNCH_CHECK(ctx);
+    return domain_h_from_coset(ctx, &key->dom, abc, m, batch, tmp, Z + key->z_h(), P + key->z_h(), key->zlen);
+}
+
+// stages the fixed entries of Z / P for a chunk whose witnesses are already at Z[p][1 .. nv]
+int stage_rows(zkb_ctx *ctx, const zkb_key *key, int batch, const Fr *d_rs, uint32_t *d_flags)
+{
+    cudaStream_t st = ctx->stream;
+    Fr *Z = ctx->scratch[SP_Z].as<Fr>(), *P = ctx->scratch[SP_P].as<Fr>();
+    ZKB_CUDA(ctx, cudaMemsetAsync(d_flags, 0, (size_t)batch * 4, st));
+    k_z_fill<<<ceil_div((size_t)batch, 64), 64, 0, st>>>(Z, key->zlen, key->nv, key->m, d_rs, batch);
+    ZKB_LAUNCH_CHECK(ctx);
+    k_z_plain<<<dim3(ceil_div(key->nv + 4, 128), batch), 128, 0, st>>>(Z, P, key->zlen, key->nv + 4);
+    ZKB_LAUNCH_CHECK(ctx);
+    return ZKB_OK;
+}
+
+int msm_and_assemble(zkb_ctx *ctx, const zkb_key *key, int batch, zkb_proof *d_out)
+{
+    const uint32_t *P = ctx->scratch[SP_P].as<uint32_t>();
+    ZKB_CUDA(ctx, ctx->scratch[SP_RES1].ensure((size_t)3 * batch * sizeof(G1X)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_RES2].ensure((size_t)batch * sizeof(G2X)));
+    G1X *r1 = ctx->scratch[SP_RES1].as<G1X>();
+    G2X *r2 = ctx->scratch[SP_RES2].as<G2X>();
+    int rc = msm_run<Fq>(ctx, &key->g1, key->g1.tab, P, key->zlen * 8, batch, r1);
+    if (!rc) rc = msm_run<Fq2>(ctx, &key->g2, key->g2.tab, P, key->zlen * 8, batch, r2);
+    if (rc) return rc;
+    k_assemble<<<batch, 64, 0, ctx->stream>>>(r1, r2, ctx->scratch[SP_P].as<Fr>(), key->zlen, key->nv, d_out);
+    ZKB_LAUNCH_CHECK(ctx);
+    return ZKB_OK;
+}
+
+} // namespace
+
+namespace {
+
+// shared body of zkb_witness_map / zkb_prove*: `dev_in` says whether w, r, s are device pointers
+int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r, const uint64_t *s,
+               bool dev_in, zkb_proof *out, uint64_t *H_out, bool map_only)
+{
+    if (!ctx || !key || !w || (!map_only && (!r || !s || !out))) return fail(ctx, ZKB_ERR_ARG, "zkb_prove: bad argument");
+    if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_prove: key lives on another device");
+    if (count == 0) return ZKB_OK;
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    cudaStream_t st = ctx->stream;
+    const size_t nv = key->nv, m = key->m, zlen = key->zlen;
+    const int chunk = chunk_size(key, count);
+    const cudaMemcpyKind kin = dev_in ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    double total_ms = 0;
+    bool unsat = false;
+    for (size_t base = 0; base < count; base += chunk) {
+        const int batch = (int)((count - base < (size_t)chunk) ? count - base : chunk);
+        ZKB_CUDA(ctx, ctx->scratch[SP_Z].ensure((size_t)batch * zlen * sizeof(Fr)));
+        ZKB_CUDA(ctx, ctx->scratch[SP_P].ensure((size_t)batch * zlen * sizeof(Fr)));
+        ZKB_CUDA(ctx, ctx->scratch[SP_RS].ensure((size_t)batch * 2 * sizeof(Fr)));
+        ZKB_CUDA(ctx, ctx->scratch[SP_FLAGS].ensure((size_t)batch * 4));
+        ZKB_CUDA(ctx, ctx->scratch[SP_PROOF].ensure((size_t)batch * sizeof(zkb_proof)));
+        Fr *Z = ctx->scratch[SP_Z].as<Fr>();
+        Fr *rs = ctx->scratch[SP_RS].as<Fr>();
+        uint32_t *flags = ctx->scratch[SP_FLAGS].as<uint32_t>();
+        zkb_proof *d_out = ctx->scratch[SP_PROOF].as<zkb_proof>();
+        if (nv)
+            ZKB_CUDA(ctx, cudaMemcpy2DAsync(Z + 1, zlen * sizeof(Fr), w + base * nv * 4, nv * sizeof(Fr), nv * sizeof(Fr), batch, kin, st));
+        if (map_only) {
+            ZKB_CUDA(ctx, cudaMemsetAsync(rs, 0, (size_t)batch * 2 * sizeof(Fr), st));
+        } else {
+            ZKB_CUDA(ctx, cudaMemcpy2DAsync(rs, 2 * sizeof(Fr), r + base * 4, sizeof(Fr), sizeof(Fr), batch, kin, st));
+            ZKB_CUDA(ctx, cudaMemcpy2DAsync(rs + 1, 2 * sizeof(Fr), s + base * 4, sizeof(Fr), sizeof(Fr), batch, kin, st));
+        }
+        ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+        int rc = stage_rows(ctx, key, batch, rs, flags);
+        if (!rc) rc = witness_map_chunk(ctx, key, batch, flags);
+        if (!rc && !map_only) rc = msm_and_assemble(ctx, key, batch, d_out);
+        if (rc) return rc;
+        ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+        const size_t pin_bytes = (size_t)batch * (sizeof(zkb_proof) + 4);
+        if (ensure_pinned(ctx, pin_bytes)) return ZKB_ERR_CUDA;
+        uint32_t *h_flags = (uint32_t *)((char *)ctx->pinned + (size_t)batch * sizeof(zkb_proof));
+        if (!map_only) ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_out, (size_t)batch * sizeof(zkb_proof), cudaMemcpyDeviceToHost, st));
+        ZKB_CUDA(ctx, cudaMemcpyAsync(h_flags, flags, (size_t)batch * 4, cudaMemcpyDeviceToHost, st));
+        if (H_out)
+            ZKB_CUDA(ctx, cudaMemcpy2DAsync(H_out + base * (m + 1) * 4, (m + 1) * sizeof(Fr), Z + key->z_h(), zlen * sizeof(Fr),
+                                            (m + 1) * sizeof(Fr), batch, cudaMemcpyDeviceToHost, st));
+        ZKB_CUDA(ctx, cudaStreamSynchronize(st));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+        total_ms += ms;
+        if (!map_only) memcpy(out + base, ctx->pinned, (size_t)batch * sizeof(zkb_proof));
+        for (int p = 0; p < batch; p++) unsat |= h_flags[p] != 0;
+    }
+    ctx->last_ms = total_ms;
+    if (unsat) return fail(ctx, ZKB_ERR_UNSAT, "the witness does not satisfy the constraint system");
+    return ZKB_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int zkb_key_upload(zkb_ctx *ctx, const zkb_key_desc *desc, zkb_key **out)
+{
+    if (!ctx || !desc || !out) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: bad argument");
+    if (!desc->alpha_g1 || !desc->beta_g1 || !desc->delta_g1 || !desc->beta_g2 || !desc->delta_g2 || !desc->A_query ||
+        !desc->H_query || (desc->B_nnz && (!desc->B_index || !desc->B_g1 || !desc->B_g2)) ||
+        (desc->num_variables > desc->num_inputs && !desc->L_query))
+        return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: missing key arrays");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    zkb_key *key = new zkb_key();
+    const int rc = key_build(ctx, desc, key);
+    if (rc) {
+        key_release(key);
+        return rc;
+    }
+    *out = key;
+    return ZKB_OK;
+}
+
+void zkb_key_free(zkb_key *key) { key_release(key); }
+
+size_t zkb_key_device_bytes(const zkb_key *key) { return key ? key->bytes : 0; }
+
+int zkb_key_domain(const zkb_key *key, size_t *m_out, int *kind_out)
+{
+    if (!key || !m_out || !kind_out) return ZKB_ERR_ARG;
+    *m_out = key->m;
+    *kind_out = key->kind;
+    return ZKB_OK;
+}
+
+int zkb_witness_map(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, uint64_t *H_out)
+{
+    if (!H_out) return fail(ctx, ZKB_ERR_ARG, "zkb_witness_map: H_out is NULL");
+    return prove_impl(ctx, key, 1, w, nullptr, nullptr, false, nullptr, H_out, true);
+}
+
+int zkb_prove(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4], zkb_proof *out,
+              uint64_t *H_out)
+{
+    return prove_impl(ctx, key, 1, w, r, s, false, out, H_out, false);
+}
+
+int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r, const uint64_t *s,
+                    zkb_proof *out)
+{
+    return prove_impl(ctx, key, count, w, r, s, false, out, nullptr, false);
+}
+
+int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const void *d_w, const void *d_r, const void *d_s,
+                           zkb_proof *out)
+{
+    return prove_impl(ctx, key, count, (const uint64_t *)d_w, (const uint64_t *)d_r, (const uint64_t *)d_s, true, out, nullptr,
+                      false);
+}
+
+} // extern "C"
