@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""bench.py -- the driver's measurement contract for the zklaim Groth16 prover backend.
+
+Workload (BASELINE.json configs[1], "zklaim main_benchmark"): a batch of 64 single-payload zklaim credential
+proofs (SHA-256 commitment + range predicate circuit: 29 356 constraints, 26 891 variables, domain 2^15) under
+one proving key, one proof stream per GPU.  A step = one batch of 64 proofs on every rank (weak scaling).
+
+  value : proofs/s, witnesses already resident in HBM (zkb_prove_batch_device), whole job
+  e2e   : proofs/s through the C ABI with HOST buffers (zkb_prove_batch: pinned witnesses in, proofs out)
+  roofline     : the dominant kernel (G1 bucket accumulation, k_accumulate<Fq>) against the measured integer
+                 multiply-add (IMAD) rate of the device -- this path is integer work, neither HBM- nor
+                 tensor-bound; its HBM fraction is reported beside it
+  cpu_baseline : the reference's own libsnark prover (oracle/_ref, -DMULTICORE -DUSE_ASM) on the host cores
+
+`--impl reference` times the reference CPU prover instead (same workload, bounded sample per step).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BATCH = 64
+WORKLOAD = "zklaim main_benchmark: batch of 64 single-payload credential proofs (Groth16, alt_bn128, 29356 constraints, domain 2^15)"
+# one Fq multiplication = 136 IMAD; a mixed addition in the reference's formulas = 11 Fq-mul
+IMAD_PER_MUL = 136
+MUL_PER_MADD_REF = 11   # madd-2007-bl as libff uses it (alt_bn128_g1.cpp:256-323)
+MUL_PER_MADD_XYZZ = 10  # madd-2008-s as the kernel executes it (ec.cuh)
+BYTES_PER_PAIR = 64 + 8  # one affine base (two 32-byte sectors) + one (entry, bucket) pair of the sorted list
+
+
+class ClockSampler(threading.Thread):
+    """samples SM clock and throttle reasons of one GPU while the timed region runs (pynvml)"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def result(self):
+        self.stop_flag = True
+        if self.is_alive():
+            self.join(1.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class stdout_to_stderr:
+    """libsnark prints progress to fd 1; the JSON line must stay alone on stdout"""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *a):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
+def reference_prover(sample):
+    """the reference's CPU prover (oracle/_ref/libzkref_mt.so: libsnark built -DMULTICORE -DUSE_ASM, all host
+    threads) on `sample` proofs of the workload.  Returns (callable running one sample -> seconds, cores, kind)"""
+    from oracle import zkref
+    import numpy as np
+    mt = zkref.available(mt=True)
+    if not (mt or zkref.available()):
+        raise RuntimeError("oracle/_ref is not built")
+    with stdout_to_stderr():
+        circ = zkref.Circuit.zklaim(1, 1, mt=mt)
+        circ.setup()
+        nv = circ.dims()["num_variables"]
+        ws = [circ.witness()]
+        if zkref.available():
+            ws += [zkref.zklaim_witness(1, 2000 + i, nv) for i in range(min(sample, 4) - 1)]
+        cores = int(zkref.lib(mt).zkref_num_threads())
+
+    def run():
+        tot = 0.0
+        with stdout_to_stderr():
+            for i in range(sample):
+                tot += circ.prove_stock(ws[i % len(ws)])
+        return tot
+
+    return run, cores, "reference"
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    sample = args.ref_sample
+    run, cores, kind = reference_prover(sample)
+    for _ in range(min(args.warmup, 1)):
+        run()
+    t = [run() for _ in range(args.steps)]
+    total = sum(t)
+    value = sample * args.steps / total
+    line = {
+        "impl": "reference", "metric": "groth16_proofs_per_s", "value": value, "unit": "proofs/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u32x8 Montgomery (254-bit integer)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": f"{sample} proofs per step on the host CPU"},
+        "cpu_baseline": {"value": value, "unit": "proofs/s", "cores": cores, "kind": kind,
+                         "sample": f"{sample * args.steps} proofs of the workload, libsnark r1cs_gg_ppzksnark_prover, OpenMP {cores} threads"},
+        "e2e": {"value": value, "unit": "proofs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "prove_ms": 1e3 * total / (sample * args.steps),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    rank, local, world = dist_env()
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    os.environ["ZKB_DEVICE"] = str(local)
+    import zklaim_b200 as zk
+    from zklaim_b200 import bridge
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- inputs: issuer setup + host-side witness generation through zklaim's own code (the bridge) ----
+    with stdout_to_stderr():
+        cred = bridge.Credentials(1, seed=1 + rank)
+        ctx, key, nv = cred.ctx, cred.key, cred.num_variables
+        nsets = 2
+        w_host = [torch.from_numpy(cred.witnesses(BATCH, 1000 + 100 * k + 10000 * rank).view(np.int64)).pin_memory() for k in range(nsets)]
+        r_host = [torch.from_numpy(cred.random_fr(BATCH).view(np.int64)).pin_memory() for _ in range(nsets)]
+        s_host = [torch.from_numpy(cred.random_fr(BATCH).view(np.int64)).pin_memory() for _ in range(nsets)]
+    w_dev = [t.cuda() for t in w_host]
+    r_dev = [t.cuda() for t in r_host]
+    s_dev = [t.cuda() for t in s_host]
+    as_u64 = lambda t: t.numpy().view(np.uint64)
+
+    def step_device(k):
+        k %= nsets
+        return ctx.prove_batch_device(key, w_dev[k].data_ptr(), r_dev[k].data_ptr(), s_dev[k].data_ptr(), BATCH)
+
+    def step_host(k):
+        k %= nsets
+        return ctx.prove_batch(key, as_u64(w_host[k]), as_u64(r_host[k]), as_u64(s_host[k]))
+
+    # sanity (outside the timed region): the reference verifier accepts what this path produces
+    proofs = step_device(0)
+    with stdout_to_stderr():
+        assert cred.verify(as_u64(w_host[0])[0], proofs[0]) and cred.verify(as_u64(w_host[0])[BATCH - 1], proofs[BATCH - 1]), \
+            "reference verifier rejected a GPU proof"
+
+    for i in range(args.warmup):
+        step_device(i)
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = ctx.kernel_launches()
+    barrier()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    for i in range(args.steps):
+        step_device(i)
+        dev_ms += ctx.last_device_ms()
+    barrier()
+    dt = max_over_ranks(time.perf_counter() - t0)
+    launches = ctx.kernel_launches() - launches0
+    clocks = sampler.result()
+    dev_ms = max_over_ranks(dev_ms)
+
+    # ---- e2e: the same steps through the C ABI with host buffers ----
+    for i in range(min(args.warmup, 3)):
+        step_host(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step_host(i)
+    barrier()
+    dt_e2e = max_over_ranks(time.perf_counter() - t0)
+
+    # ---- single-proof latency (prove ms) ----
+    lat = []
+    w1, r1, s1 = as_u64(w_host[0])[0], as_u64(r_host[0])[0], as_u64(s_host[0])[0]
+    for i in range(7):
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        ctx.prove(key, w1, r1, s1)
+        lat.append(1e3 * (time.perf_counter() - t))
+    prove_ms = sorted(lat)[len(lat) // 2]
+
+    # ---- roofline of the dominant kernel: CUDA events around k_accumulate<Fq> on the library's stream ----
+    ctx.profile(True)
+    for i in range(3):
+        step_device(i)
+    prof = ctx.profile_read()
+    ctx.profile(False)
+
+    if rank != 0:
+        return
+    peaks, peak_kind = measured_peaks()
+    imad_peak = ctx.imad_peak(8192)
+    acc_s = prof["g1_ms"] * 1e-3 / max(prof["g1_launches"], 1)
+    pairs = prof["g1_pairs"] / max(prof["g1_launches"], 1)
+    achieved = pairs * MUL_PER_MADD_REF * IMAD_PER_MUL / acc_s
+    roofline = {
+        "bound": "imad", "kernel": "k_accumulate<Fq> (G1 bucket accumulation)",
+        "achieved": achieved / 1e9, "peak": imad_peak / 1e9, "unit": "GIMAD/s", "frac": achieved / imad_peak,
+        "peak_source": "mad.wide.u32 chains on all SMs, measured live (zkb_measure_imad_peak)",
+        "achieved_executed": pairs * MUL_PER_MADD_XYZZ * IMAD_PER_MUL / acc_s / 1e9,
+        "units_per_launch": pairs, "ms_per_launch": acc_s * 1e3, "traffic": None,
+        "hbm": {"achieved": pairs * BYTES_PER_PAIR / acc_s / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": pairs * BYTES_PER_PAIR / acc_s / 1e9 / peaks["hbm_gbs"], "peak_source": peak_kind},
+        "step_share": prof["g1_ms"] / max(prof["g1_launches"], 1) / (dev_ms / args.steps),
+    }
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            run, cores, kind = reference_prover(args.ref_sample)
+            sec = run()
+            cpu = {"value": args.ref_sample / sec, "unit": "proofs/s", "cores": cores, "kind": kind,
+                   "sample": f"{args.ref_sample} proofs of the workload, libsnark r1cs_gg_ppzksnark_prover (-DMULTICORE -DUSE_ASM), OpenMP {cores} threads",
+                   "prove_ms": 1e3 * sec / args.ref_sample}
+        except Exception as e:  # the GPU numbers stand on their own
+            cpu = {"unavailable": str(e)}
+    total = BATCH * args.steps * world
+    line = {
+        "metric": "groth16_proofs_per_s", "value": total / dt, "unit": "proofs/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32x8 Montgomery (254-bit integer)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "parallelism": f"one proof stream per GPU x{world}",
+                   "l2": f"{nsets} input sets alternate; key + scratch working set (> 1 GB) exceeds the 126 MB L2, no flush",
+                   "inputs": "seeded synthetic credentials (salts), witnesses generated by zklaim's gadget code on the host"},
+        "device_ms_per_step": dev_ms / args.steps,
+        "prove_ms": prove_ms,
+        "e2e": {"value": total / dt_e2e, "unit": "proofs/s", "h2d_bytes_per_step": BATCH * (nv * 32 + 64),
+                "d2h_bytes_per_step": BATCH * (384 + 4), "ms_per_step": 1e3 * dt_e2e / args.steps},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "key_device_mb": key.device_bytes() / 1e6,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--ref-sample", type=int, default=8, help="proofs per step of the CPU reference arm / cpu_baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,293 @@
+/*
+ * zkb_libsnark.hpp -- host-side adapter between libsnark's r1cs_gg_ppzksnark types and the zkb C ABI
+ * (include/zkb.h).  This is the code a zklaim maintainer adds to the tree: with it,
+ *
+ *     zklaim/snark.cpp:126
+ *         return r1cs_gg_ppzksnark_prover<ppT>(proving_key, pb.primary_input(), pb.auxiliary_input());
+ * becomes
+ *         return zkb_bridge::prover<ppT>(proving_key, pb.primary_input(), pb.auxiliary_input());
+ *
+ * with the same signature and return type (r1cs_gg_ppzksnark.hpp:373-376).  Everything else of
+ * zklaim (C API, gadgets, key / proof serialisation, verifier) is untouched.
+ *
+ * The adapter is header-only and is compiled together with the reference's own headers; it
+ * contains no arithmetic: it flattens the proving key into the arrays of zkb_key_desc
+ * (affine Montgomery limbs, CSR matrices), keeps the uploaded key cached per device, draws the
+ * blinding scalars exactly where the reference does (r1cs_gg_ppzksnark.tcc:418-419,
+ * Fr::random_element) and wraps the three returned points into r1cs_gg_ppzksnark_proof.
+ * Only alt_bn128 (the curve zklaim is built for, zklaim/snark.cpp ppT) is supported.
+ */
+#ifndef ZKB_LIBSNARK_HPP
+#define ZKB_LIBSNARK_HPP
+
+#include <cstring>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
+#include <libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.hpp>
+
+#include "../include/zkb.h"
+
+namespace zkb_bridge {
+
+typedef libff::alt_bn128_pp PP;
+typedef libff::Fr<PP> FrT;
+typedef libff::G1<PP> G1T;
+typedef libff::G2<PP> G2T;
+
+inline void put_fp(uint64_t *dst, const libff::alt_bn128_Fq &x) { memcpy(dst, x.mont_repr.data, 32); }
+inline void put_fr(uint64_t *dst, const FrT &x) { memcpy(dst, x.mont_repr.data, 32); }
+inline libff::alt_bn128_Fq get_fp(const uint64_t *src)
+{
+    libff::alt_bn128_Fq x;
+    memcpy(x.mont_repr.data, src, 32);
+    return x;
+}
+
+/* affine limbs of a key element; zero -> all-zero limbs (include/zkb.h conventions) */
+inline void put_g1_affine(uint64_t *dst, const G1T &p)
+{
+    if (p.is_zero()) {
+        memset(dst, 0, 64);
+        return;
+    }
+    if (p.Z == libff::alt_bn128_Fq::one()) { /* the form operator>> leaves (alt_bn128_g1.cpp:453-462) */
+        put_fp(dst, p.X);
+        put_fp(dst + 4, p.Y);
+        return;
+    }
+    G1T c(p);
+    c.to_affine_coordinates();
+    put_fp(dst, c.X);
+    put_fp(dst + 4, c.Y);
+}
+inline void put_g2_affine(uint64_t *dst, const G2T &p)
+{
+    if (p.is_zero()) {
+        memset(dst, 0, 128);
+        return;
+    }
+    G2T c(p);
+    if (!(c.Z == libff::alt_bn128_Fq2::one())) c.to_affine_coordinates();
+    put_fp(dst, c.X.c0);
+    put_fp(dst + 4, c.X.c1);
+    put_fp(dst + 8, c.Y.c0);
+    put_fp(dst + 12, c.Y.c1);
+}
+inline G1T get_g1_jacobian(const uint64_t *src) { return G1T(get_fp(src), get_fp(src + 4), get_fp(src + 8)); }
+inline G2T get_g2_jacobian(const uint64_t *src)
+{
+    return G2T(libff::alt_bn128_Fq2(get_fp(src), get_fp(src + 4)), libff::alt_bn128_Fq2(get_fp(src + 8), get_fp(src + 12)),
+               libff::alt_bn128_Fq2(get_fp(src + 16), get_fp(src + 20)));
+}
+
+/* flat copy of a proving key; owns the storage the zkb_key_desc points into */
+struct KeyArrays {
+    std::vector<uint64_t> row_ptr[3], coeff[3];
+    std::vector<uint32_t> col[3];
+    std::vector<uint64_t> singles, A, B1, B2, H, L;
+    std::vector<uint32_t> B_idx;
+    zkb_key_desc desc;
+};
+
+inline void pack_matrix(const libsnark::r1cs_constraint_system<FrT> &cs, int which, KeyArrays &k)
+{
+    std::vector<uint64_t> &rp = k.row_ptr[which];
+    rp.assign(1, 0);
+    for (const auto &c : cs.constraints) {
+        const libsnark::linear_combination<FrT> &lc = which == 0 ? c.a : (which == 1 ? c.b : c.c);
+        for (const auto &t : lc.terms) {
+            k.col[which].push_back((uint32_t)t.index);
+            const size_t o = k.coeff[which].size();
+            k.coeff[which].resize(o + 4);
+            put_fr(&k.coeff[which][o], t.coeff);
+        }
+        rp.push_back(k.col[which].size());
+    }
+}
+
+inline void pack_proving_key(const libsnark::r1cs_gg_ppzksnark_proving_key<PP> &pk, KeyArrays &k)
+{
+    const libsnark::r1cs_constraint_system<FrT> &cs = pk.constraint_system;
+    for (int w = 0; w < 3; w++) pack_matrix(cs, w, k);
+    k.singles.resize(8 * 3 + 16 * 2);
+    put_g1_affine(&k.singles[0], pk.alpha_g1);
+    put_g1_affine(&k.singles[8], pk.beta_g1);
+    put_g1_affine(&k.singles[16], pk.delta_g1);
+    put_g2_affine(&k.singles[24], pk.beta_g2);
+    put_g2_affine(&k.singles[40], pk.delta_g2);
+    k.A.resize(pk.A_query.size() * 8);
+    for (size_t i = 0; i < pk.A_query.size(); i++) put_g1_affine(&k.A[8 * i], pk.A_query[i]);
+    const size_t nb = pk.B_query.indices.size();
+    k.B1.resize(nb * 8 + 8);
+    k.B2.resize(nb * 16 + 16);
+    k.B_idx.resize(nb + 1);
+    for (size_t i = 0; i < nb; i++) {
+        k.B_idx[i] = (uint32_t)pk.B_query.indices[i];
+        put_g1_affine(&k.B1[8 * i], pk.B_query.values[i].h);
+        put_g2_affine(&k.B2[16 * i], pk.B_query.values[i].g);
+    }
+    k.H.resize(pk.H_query.size() * 8 + 8);
+    for (size_t i = 0; i < pk.H_query.size(); i++) put_g1_affine(&k.H[8 * i], pk.H_query[i]);
+    k.L.resize(pk.L_query.size() * 8 + 8);
+    for (size_t i = 0; i < pk.L_query.size(); i++) put_g1_affine(&k.L[8 * i], pk.L_query[i]);
+
+    zkb_key_desc &d = k.desc;
+    memset(&d, 0, sizeof(d));
+    d.num_constraints = cs.num_constraints();
+    d.num_variables = cs.num_variables();
+    d.num_inputs = cs.num_inputs();
+    zkb_csr *m[3] = {&d.A, &d.B, &d.C};
+    for (int w = 0; w < 3; w++) {
+        m[w]->row_ptr = k.row_ptr[w].data();
+        m[w]->col = k.col[w].data();
+        m[w]->coeff = k.coeff[w].data();
+    }
+    d.alpha_g1 = &k.singles[0];
+    d.beta_g1 = &k.singles[8];
+    d.delta_g1 = &k.singles[16];
+    d.beta_g2 = &k.singles[24];
+    d.delta_g2 = &k.singles[40];
+    d.A_query = k.A.data();
+    d.B_nnz = nb;
+    d.B_index = k.B_idx.data();
+    d.B_g1 = k.B1.data();
+    d.B_g2 = k.B2.data();
+    d.H_size = pk.H_query.size();
+    d.H_query = k.H.data();
+    d.L_query = k.L.data();
+}
+
+/* 64-bit FNV-1a */
+inline uint64_t fnv1a(const void *p, size_t n, uint64_t h = 0xcbf29ce484222325ull)
+{
+    const unsigned char *b = (const unsigned char *)p;
+    for (size_t i = 0; i < n; i++) h = (h ^ b[i]) * 0x100000001b3ull;
+    return h;
+}
+
+/* identifies a proving key without walking all of it: sizes, the five single elements and probes of the queries */
+inline uint64_t key_fingerprint(const libsnark::r1cs_gg_ppzksnark_proving_key<PP> &pk)
+{
+    uint64_t buf[64];
+    size_t n = 0;
+    buf[n++] = pk.constraint_system.num_constraints();
+    buf[n++] = pk.constraint_system.num_variables();
+    buf[n++] = pk.constraint_system.num_inputs();
+    buf[n++] = pk.A_query.size();
+    buf[n++] = pk.B_query.indices.size();
+    buf[n++] = pk.H_query.size();
+    buf[n++] = pk.L_query.size();
+    uint64_t h = fnv1a(buf, n * 8);
+    auto mix_g1 = [&](const G1T &p) {
+        uint64_t t[8];
+        put_g1_affine(t, p);
+        h = fnv1a(t, 64, h);
+    };
+    mix_g1(pk.alpha_g1);
+    mix_g1(pk.beta_g1);
+    mix_g1(pk.delta_g1);
+    uint64_t t2[16];
+    put_g2_affine(t2, pk.delta_g2);
+    h = fnv1a(t2, 128, h);
+    if (!pk.A_query.empty()) mix_g1(pk.A_query.back());
+    if (!pk.H_query.empty()) {
+        mix_g1(pk.H_query.front());
+        mix_g1(pk.H_query.back());
+    }
+    if (!pk.L_query.empty()) mix_g1(pk.L_query.back());
+    return h;
+}
+
+/* One zkb context per device plus the uploaded keys, for the lifetime of the process.  zklaim's bridge is
+ * single-threaded (libsnark_wrapper.cpp re-initialises the curve globals per call), so is this cache. */
+class Session {
+  public:
+    static Session &get()
+    {
+        static Session s;
+        return s;
+    }
+    zkb_ctx *ctx()
+    {
+        if (!ctx_) {
+            const char *dev = getenv("ZKB_DEVICE");
+            if (zkb_init(dev ? atoi(dev) : 0, &ctx_) != ZKB_OK)
+                throw std::runtime_error(std::string("zkb_init failed: ") + zkb_last_error(NULL));
+        }
+        return ctx_;
+    }
+    /* returns the cached device key for `id`, or uploads it with `make` */
+    template <class PackFn> const zkb_key *key(uint64_t id, PackFn pack)
+    {
+        auto it = keys_.find(id);
+        if (it != keys_.end()) return it->second;
+        std::unique_ptr<KeyArrays> arrays(new KeyArrays());
+        pack(*arrays);
+        zkb_key *k = NULL;
+        if (zkb_key_upload(ctx(), &arrays->desc, &k) != ZKB_OK)
+            throw std::runtime_error(std::string("zkb_key_upload failed: ") + zkb_last_error(ctx_));
+        keys_[id] = k;
+        return k;
+    }
+    bool has_key(uint64_t id) const { return keys_.count(id) != 0; }
+    void clear()
+    {
+        for (auto &kv : keys_) zkb_key_free(kv.second);
+        keys_.clear();
+        if (ctx_) zkb_shutdown(ctx_);
+        ctx_ = NULL;
+    }
+    ~Session() { clear(); }
+
+  private:
+    zkb_ctx *ctx_ = NULL;
+    std::map<uint64_t, zkb_key *> keys_;
+};
+
+inline libsnark::r1cs_gg_ppzksnark_proof<PP> wrap_proof(const zkb_proof &p)
+{
+    G1T A = get_g1_jacobian(p.A);
+    G2T B = get_g2_jacobian(p.B);
+    G1T C = get_g1_jacobian(p.C);
+    return libsnark::r1cs_gg_ppzksnark_proof<PP>(std::move(A), std::move(B), std::move(C));
+}
+
+/* full variable assignment as the contiguous limb array zkb_prove expects (Fp_model is 32 bytes, fp.hpp:42) */
+inline void pack_assignment(const std::vector<FrT> &primary, const std::vector<FrT> &auxiliary, uint64_t *dst)
+{
+    for (size_t i = 0; i < primary.size(); i++) put_fr(dst + 4 * i, primary[i]);
+    for (size_t i = 0; i < auxiliary.size(); i++) put_fr(dst + 4 * (primary.size() + i), auxiliary[i]);
+}
+
+/* the prover with the blinding scalars given (tests fix them; the drop-in below draws them) */
+inline libsnark::r1cs_gg_ppzksnark_proof<PP> prover_with_rs(const zkb_key *key, const std::vector<FrT> &primary,
+                                                           const std::vector<FrT> &auxiliary, const FrT &r, const FrT &s)
+{
+    std::vector<uint64_t> w(4 * (primary.size() + auxiliary.size()));
+    pack_assignment(primary, auxiliary, w.data());
+    zkb_proof out;
+    zkb_ctx *ctx = Session::get().ctx();
+    const int rc = zkb_prove(ctx, key, w.data(), (const uint64_t *)r.mont_repr.data, (const uint64_t *)s.mont_repr.data, &out, NULL);
+    if (rc != ZKB_OK) throw std::runtime_error(std::string("zkb_prove failed: ") + zkb_last_error(ctx));
+    return wrap_proof(out);
+}
+
+/* Drop-in for r1cs_gg_ppzksnark_prover<alt_bn128_pp> (r1cs_gg_ppzksnark.tcc:390-505). */
+template <typename ppT>
+libsnark::r1cs_gg_ppzksnark_proof<ppT> prover(const libsnark::r1cs_gg_ppzksnark_proving_key<ppT> &pk,
+                                              const libsnark::r1cs_gg_ppzksnark_primary_input<ppT> &primary_input,
+                                              const libsnark::r1cs_gg_ppzksnark_auxiliary_input<ppT> &auxiliary_input)
+{
+    static_assert(std::is_same<ppT, PP>::value, "the zkb backend implements alt_bn128 only");
+    const zkb_key *key = Session::get().key(key_fingerprint(pk), [&](KeyArrays &k) { pack_proving_key(pk, k); });
+    const FrT r = FrT::random_element(), s = FrT::random_element(); /* r1cs_gg_ppzksnark.tcc:418-419 */
+    return prover_with_rs(key, primary_input, auxiliary_input, r, s);
+}
+
+} // namespace zkb_bridge
+#endif /* ZKB_LIBSNARK_HPP */

@@ -183,6 +183,11 @@ int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const
 double zkb_measure_imad_peak(zkb_ctx *ctx, int iters);
 /* Device milliseconds (CUDA events on the context's stream) of the kernels launched by the most
  * recent zkb_msm* / zkb_witness_map / zkb_prove* call, and how many kernels that was. */
+/* Live timing of the dominant kernel (bucket accumulation) with CUDA events on the context's stream.
+ * zkb_profile(ctx, 1) resets and enables it; out = {G1 ms, G1 launches, G1 pairs, G2 ms, G2 launches, G2 pairs}
+ * summed over the calls since; a "pair" is one mixed addition of a base into a bucket. */
+int zkb_profile(zkb_ctx *ctx, int enable);
+int zkb_profile_read(const zkb_ctx *ctx, double out[6]);
 double zkb_last_device_ms(const zkb_ctx *ctx);
 long zkb_last_kernel_launches(const zkb_ctx *ctx);
 

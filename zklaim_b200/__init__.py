@@ -59,6 +59,8 @@ SYMBOLS = {
     "zkb_prove_batch": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p, _vp]),
     "zkb_prove_batch_device": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
     "zkb_measure_imad_peak": (C.c_double, [_vp, _i]),
+    "zkb_profile": (_i, [_vp, _i]),
+    "zkb_profile_read": (_i, [_vp, C.POINTER(C.c_double)]),
     "zkb_last_device_ms": (C.c_double, [_vp]),
     "zkb_last_kernel_launches": (C.c_long, [_vp]),
 }
@@ -135,10 +137,20 @@ class Context:
         self.h = h
         self.device = device
 
+    @classmethod
+    def from_handle(cls, handle) -> "Context":
+        """View of a zkb_ctx that somebody else owns (the bridge's); never shut down from here."""
+        self = cls.__new__(cls)
+        self.lib = load_library()
+        self.h = C.c_void_p(handle)
+        self.device = -1
+        self.borrowed = True
+        return self
+
     def close(self):
-        if getattr(self, "h", None):
+        if getattr(self, "h", None) and not getattr(self, "borrowed", False):
             self.lib.zkb_shutdown(self.h)
-            self.h = None
+        self.h = None
 
     def __del__(self):
         try:
@@ -264,17 +276,26 @@ class Context:
         assert w.shape[0] == count and s.shape[0] == count
         out = (Proof * count)()
         self._chk(self.lib.zkb_prove_batch(self.h, key.h, count, w.ctypes.data, r.ctypes.data, s.ctypes.data, out))
-        return np.stack([p.as_array() for p in out])
+        return np.frombuffer(out, dtype=np.uint64).reshape(count, 48).copy()
 
     def prove_batch_device(self, key: "Key", d_w: int, d_r: int, d_s: int, count: int) -> np.ndarray:
         """w, r, s are CUDA device pointers (e.g. torch tensors' data_ptr()) on this context's device."""
         out = (Proof * count)()
         self._chk(self.lib.zkb_prove_batch_device(self.h, key.h, count, d_w, d_r, d_s, out))
-        return np.stack([p.as_array() for p in out])
+        return np.frombuffer(out, dtype=np.uint64).reshape(count, 48).copy()
 
     # ---- measurement ------------------------------------------------------------------
     def imad_peak(self, iters: int = 4096) -> float:
         return float(self.lib.zkb_measure_imad_peak(self.h, iters))
+
+    def profile(self, enable: bool = True):
+        self._chk(self.lib.zkb_profile(self.h, int(enable)))
+
+    def profile_read(self) -> dict:
+        out = (C.c_double * 6)()
+        self._chk(self.lib.zkb_profile_read(self.h, out))
+        return {"g1_ms": out[0], "g1_launches": int(out[1]), "g1_pairs": out[2],
+                "g2_ms": out[3], "g2_launches": int(out[4]), "g2_pairs": out[5]}
 
     def last_device_ms(self) -> float:
         return float(self.lib.zkb_last_device_ms(self.h))

@@ -1,0 +1,99 @@
+"""ctypes binding of bridge/_build/libzkb_zklaim.so -- zklaim's own host code (credential gadgets, trusted
+setup, (de)serialisation, verifier: compiled in place from the reference tree by bridge/Makefile) with the
+Groth16 prover replaced by libzkb.so.  See bridge/zkb_zklaim_bridge.cpp and INTEGRATION.md.
+
+This is the host side of the drop-in: the GPU never sees anything but what zkb.h describes.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import Context, Key, Proof, ZkbError, load_library
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "bridge", "_build", "libzkb_zklaim.so")
+_vp, _sz, _u64, _i = C.c_void_p, C.c_size_t, C.c_uint64, C.c_int
+_SIG = {
+    "zkb_libsnark_prove": (_i, [_vp]),
+    "zkb_libsnark_prove_batch": (_i, [_vp, _sz]),
+    "zkb_bridge_reset": (None, []),
+    "zkbr_new": (_vp, [_sz, _u64]),
+    "zkbr_free": (None, [_vp]),
+    "zkbr_dims": (None, [_vp, _vp]),
+    "zkbr_key": (_vp, [_vp]),
+    "zkbr_ctx": (_vp, []),
+    "zkbr_witnesses": (_i, [_vp, _sz, _u64, _vp]),
+    "zkbr_random_fr": (None, [_sz, _vp]),
+    "zkbr_verify": (_i, [_vp, _vp, _vp]),
+    "zkbr_roundtrip": (_i, [_vp, _sz, _u64, _vp]),
+}
+_lib = None
+
+
+def available() -> bool:
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not available():
+            raise ZkbError(-1, f"{LIB_PATH} not built (make -C bridge; needs the reference tree)")
+        load_library()  # libzkb.so first, so that the bridge binds to the same copy
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIG.items():
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+class Credentials:
+    """A zklaim deployment: one issuer setup for `payloads`-payload credentials, its key resident on the GPU."""
+
+    def __init__(self, payloads: int = 1, seed: int = 1):
+        self.L = lib()
+        self.h = self.L.zkbr_new(payloads, seed)
+        if not self.h:
+            raise ZkbError(-1, "bridge setup failed (no GPU, or trusted setup error)")
+        d = (C.c_size_t * 6)()
+        self.L.zkbr_dims(self.h, d)
+        self.num_variables, self.num_inputs, self.pk_bytes, self.vk_bytes = [int(x) for x in d[:4]]
+        self.setup_s, self.import_upload_s = d[4] / 1e6, d[5] / 1e6
+        self.payloads = payloads
+        # the bridge's own zkb context / device key, viewed through the Python mirror
+        self.ctx = Context.from_handle(self.L.zkbr_ctx())
+        self.key = Key(self.ctx, C.c_void_p(self.L.zkbr_key(self.h)), self.num_variables)
+
+    def witnesses(self, count: int, seed0: int = 1000) -> np.ndarray:
+        w = np.zeros((count, self.num_variables, 4), dtype=np.uint64)
+        rc = self.L.zkbr_witnesses(self.h, count, seed0, w.ctypes.data)
+        if rc:
+            raise ZkbError(rc, "witness generation failed")
+        return w
+
+    def random_fr(self, count: int) -> np.ndarray:
+        out = np.zeros((count, 4), dtype=np.uint64)
+        self.L.zkbr_random_fr(count, out.ctypes.data)
+        return out
+
+    def verify(self, w: np.ndarray, proof: np.ndarray) -> bool:
+        w = np.ascontiguousarray(w, dtype=np.uint64)
+        p = np.ascontiguousarray(proof, dtype=np.uint64)
+        assert p.size == 48
+        return bool(self.L.zkbr_verify(self.h, w.ctypes.data, p.ctypes.data))
+
+    def roundtrip(self, count: int, seed0: int = 5000):
+        """count credentials through zkb_libsnark_prove(_batch) and the reference's libsnark_verify.
+        Returns (accepted, prove_seconds, verify_seconds)."""
+        t = (C.c_double * 2)()
+        ok = self.L.zkbr_roundtrip(self.h, count, seed0, t)
+        return ok, t[0], t[1]
+
+    def close(self):
+        if self.h:
+            self.L.zkbr_free(self.h)
+            self.h = None

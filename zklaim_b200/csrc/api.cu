@@ -19,6 +19,20 @@ int ensure_pinned(zkb_ctx *ctx, size_t bytes)
     ctx->pinned_cap = want;
     return 0;
 }
+void prof_collect(zkb_ctx *ctx)
+{
+    if (!ctx->prof) return;
+    for (int g = 0; g < 2; g++) {
+        if (!ctx->prof_pending[g]) continue;
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, ctx->pe[g][0], ctx->pe[g][1]) == cudaSuccess) {
+            ctx->prof_ms[g] += ms;
+            ctx->prof_launches[g]++;
+            ctx->prof_pairs[g] += ctx->prof_pairs_host[g];
+        }
+        ctx->prof_pending[g] = false;
+    }
+}
 } // namespace zkb
 
 using namespace zkb;
@@ -81,6 +95,11 @@ void zkb_shutdown(zkb_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     for (auto &s : ctx->scratch) s.release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->prof_pairs_host) {
+        cudaFreeHost(ctx->prof_pairs_host);
+        for (int g = 0; g < 2; g++)
+            for (int k = 0; k < 2; k++) cudaEventDestroy(ctx->pe[g][k]);
+    }
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);
@@ -88,6 +107,35 @@ void zkb_shutdown(zkb_ctx *ctx)
 }
 
 const char *zkb_last_error(const zkb_ctx *ctx) { return ctx ? ctx->err.c_str() : g_init_err.c_str(); }
+
+int zkb_profile(zkb_ctx *ctx, int enable)
+{
+    if (!ctx) return ZKB_ERR_ARG;
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    if (enable && !ctx->prof_pairs_host) {
+        for (int g = 0; g < 2; g++)
+            for (int k = 0; k < 2; k++) ZKB_CUDA(ctx, cudaEventCreate(&ctx->pe[g][k]));
+        ZKB_CUDA(ctx, cudaMallocHost((void **)&ctx->prof_pairs_host, 16));
+    }
+    ctx->prof = enable != 0;
+    for (int g = 0; g < 2; g++) {
+        ctx->prof_ms[g] = ctx->prof_pairs[g] = 0;
+        ctx->prof_launches[g] = 0;
+        ctx->prof_pending[g] = false;
+    }
+    return ZKB_OK;
+}
+
+int zkb_profile_read(const zkb_ctx *ctx, double out[6])
+{
+    if (!ctx || !out) return ZKB_ERR_ARG;
+    for (int g = 0; g < 2; g++) {
+        out[3 * g] = ctx->prof_ms[g];
+        out[3 * g + 1] = (double)ctx->prof_launches[g];
+        out[3 * g + 2] = ctx->prof_pairs[g];
+    }
+    return ZKB_OK;
+}
 
 double zkb_last_device_ms(const zkb_ctx *ctx) { return ctx ? ctx->last_ms : -1.0; }
 long zkb_last_kernel_launches(const zkb_ctx *ctx) { return ctx ? ctx->launches : -1; }

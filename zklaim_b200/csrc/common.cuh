@@ -50,6 +50,13 @@ struct zkb_ctx {
     zkb::DevBuf scratch[64];
     void *pinned = nullptr; // small pinned staging area for results
     size_t pinned_cap = 0;
+    // optional profiling of the dominant kernel (bucket accumulation), per group: [0] = G1, [1] = G2
+    bool prof = false;
+    cudaEvent_t pe[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+    uint32_t *prof_pairs_host = nullptr; // pinned, 2 words
+    bool prof_pending[2] = {false, false};
+    double prof_ms[2] = {0, 0}, prof_pairs[2] = {0, 0};
+    long prof_launches[2] = {0, 0};
 };
 
 namespace zkb {
@@ -127,5 +134,7 @@ inline unsigned ceil_div(size_t a, size_t b) { return (unsigned)((a + b - 1) / b
 
 // host-side helpers implemented in api.cu
 int ensure_pinned(zkb_ctx *ctx, size_t bytes);
+// folds the event pairs recorded since the last call into the profile counters (stream must be idle)
+void prof_collect(zkb_ctx *ctx);
 
 } // namespace zkb

@@ -349,11 +349,20 @@ int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_PARTS].ensure(2 * (runs + 1) * sizeof(PT)));
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_BUCKETS].ensure(B * sizeof(PT)));
     if (runs) {
+        const int g = plan->group == ZKB_G2 ? 1 : 0;
+        const bool prof = ctx->prof && !ctx->prof_pending[g]; // one sample per synchronisation
+        if (prof) ZKB_CUDA(ctx, cudaEventRecord(ctx->pe[g][0], ctx->stream));
         rc = launch_accumulate<F>(ctx, (const Affine<F> *)plan->d_pts, ctx->scratch[gs + SB_ENT].as<uint32_t>(),
                                   ctx->scratch[gs + SB_EBKT].as<uint32_t>(), ctx->scratch[gs + SB_START].as<uint32_t>(),
                                   (uint32_t)B, S, ctx->scratch[gs + SB_BUCKETS].as<PT>(),
                                   ctx->scratch[gs + SB_PARTS].as<PT>(), runs);
         if (rc) return rc;
+        if (prof) {
+            ZKB_CUDA(ctx, cudaEventRecord(ctx->pe[g][1], ctx->stream));
+            ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->prof_pairs_host + g, ctx->scratch[gs + SB_START].as<uint32_t>() + B, 4,
+                                          cudaMemcpyDeviceToHost, ctx->stream));
+            ctx->prof_pending[g] = true;
+        }
     }
     return msm_finish<F>(ctx, plan, tab, batch, S, d_res);
 }

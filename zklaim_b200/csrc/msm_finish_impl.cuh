@@ -281,6 +281,7 @@ template <class F> int results_to_host(zkb_ctx *ctx, const XYZZ<F> *d_res, size_
     float ms = 0;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_ms = ms;
+    prof_collect(ctx);
     memcpy(out_jacobian, ctx->pinned, bytes);
     return ZKB_OK;
 }

@@ -439,6 +439,7 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
         float ms = 0;
         cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
         total_ms += ms;
+        prof_collect(ctx);
         if (!map_only) memcpy(out + base, ctx->pinned, (size_t)batch * sizeof(zkb_proof));
         for (int p = 0; p < batch; p++) unsat |= h_flags[p] != 0;
     }
