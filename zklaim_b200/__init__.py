@@ -224,7 +224,7 @@ class Context:
 
     # ---- key / prover -----------------------------------------------------------------
     def upload_key(self, key: dict) -> "Key":
-        """key: dict with the fields of zkb_key_desc as numpy arrays (see oracle.zkref.export_key)."""
+        """key: dict with the fields of zkb_key_desc as numpy arrays (bridge: zkb_libsnark.hpp flattens a libsnark proving key into them)."""
         keep = []
 
         def ptr(a, dtype=np.uint64):
