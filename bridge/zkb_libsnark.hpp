@@ -23,6 +23,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <set>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -235,10 +236,18 @@ class Session {
         return k;
     }
     bool has_key(uint64_t id) const { return keys_.count(id) != 0; }
+    /* first witness seen for a key: size its MSM windows for that witness's 0 / 1 statistics (zkb_key_tune) */
+    void tune_once(const zkb_key *key, const uint64_t *w)
+    {
+        if (!tuned_.insert(key).second) return;
+        if (zkb_key_tune(ctx(), const_cast<zkb_key *>(key), w) != ZKB_OK)
+            throw std::runtime_error(std::string("zkb_key_tune failed: ") + zkb_last_error(ctx_));
+    }
     void clear()
     {
         for (auto &kv : keys_) zkb_key_free(kv.second);
         keys_.clear();
+        tuned_.clear();
         if (ctx_) zkb_shutdown(ctx_);
         ctx_ = NULL;
     }
@@ -247,6 +256,7 @@ class Session {
   private:
     zkb_ctx *ctx_ = NULL;
     std::map<uint64_t, zkb_key *> keys_;
+    std::set<const zkb_key *> tuned_;
 };
 
 inline libsnark::r1cs_gg_ppzksnark_proof<PP> wrap_proof(const zkb_proof &p)
@@ -270,6 +280,7 @@ inline libsnark::r1cs_gg_ppzksnark_proof<PP> prover_with_rs(const zkb_key *key, 
 {
     std::vector<uint64_t> w(4 * (primary.size() + auxiliary.size()));
     pack_assignment(primary, auxiliary, w.data());
+    Session::get().tune_once(key, w.data());
     zkb_proof out;
     zkb_ctx *ctx = Session::get().ctx();
     const int rc = zkb_prove(ctx, key, w.data(), (const uint64_t *)r.mont_repr.data, (const uint64_t *)s.mont_repr.data, &out, NULL);

@@ -123,6 +123,7 @@ int zkb_libsnark_prove_batch(zklaim_ctx **ctxs, size_t n)
             put_fr(&r[4 * i], FrT::random_element());
             put_fr(&s[4 * i], FrT::random_element());
         }
+        Session::get().tune_once(ck.key, w.data());
         std::vector<zkb_proof> out(n);
         zkb_ctx *z = Session::get().ctx();
         if (zkb_prove_batch(z, ck.key, n, w.data(), r.data(), s.data(), out.data()) != ZKB_OK) {
@@ -260,6 +261,7 @@ int zkbr_witnesses(void *h, size_t count, uint64_t seed0, uint64_t *w_out)
         if (!build_witness(&c.ctx, primary, auxiliary)) return 1;
         if (primary.size() + auxiliary.size() != nv) return 2;
         pack_assignment(primary, auxiliary, w_out + i * nv * 4);
+        if (i == 0) Session::get().tune_once(b->key.key, w_out);
     }
     return 0;
 }

@@ -145,6 +145,14 @@ typedef struct {
 int zkb_key_upload(zkb_ctx *ctx, const zkb_key_desc *desc, zkb_key **out);
 void zkb_key_free(zkb_key *key);
 size_t zkb_key_device_bytes(const zkb_key *key);
+/* Re-plans the MSM window widths of the key for the scalar statistics of a sample witness w (num_variables x 4
+ * limbs): Groth16 witnesses are dominated by 0 / 1 values, which the reference special-cases in
+ * multi_exp_with_mixed_addition (multiexp.tcc:466-481); here they cost one bucket entry whatever the window, so
+ * the windows are sized for the remaining dense scalars.  Proofs are unchanged (any window gives the same group
+ * element); only speed and device memory change.  Must not run concurrently with proofs that use this key. */
+int zkb_key_tune(zkb_ctx *ctx, zkb_key *key, const uint64_t *w);
+/* window bits currently planned for the A, B-in-G1, H + L and B-in-G2 queries */
+int zkb_key_windows(const zkb_key *key, int out[4]);
 /* domain chosen for this key (what r1cs_to_qap_witness_map would use, r1cs_to_qap.tcc:218) */
 int zkb_key_domain(const zkb_key *key, size_t *m_out, int *kind_out);
 
@@ -178,8 +186,9 @@ int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const
                            const void *d_s, zkb_proof *out);
 
 /* ---- measurement helpers (used by bench.py only) ------------------------------------ */
-/* Sustained integer multiply-add rate of the device: independent mad.wide.u32 chains on all
- * SMs; returns 32x32+64->64 multiply-adds per second, or < 0 on error. */
+/* Sustained integer multiply-add rate of the device, measured with chains of dependent Fq Montgomery
+ * products (136 multiply-adds of 32 x 32 + 64 -> 64 bits each, the instruction mix of every kernel here) on
+ * all SMs; `iters` = products per chain / 2 (0 = default).  Returns multiply-adds per second, < 0 on error. */
 double zkb_measure_imad_peak(zkb_ctx *ctx, int iters);
 /* Device milliseconds (CUDA events on the context's stream) of the kernels launched by the most
  * recent zkb_msm* / zkb_witness_map / zkb_prove* call, and how many kernels that was. */

@@ -18,6 +18,10 @@ key = ctx.upload_key(kd)
 print(f"key upload {time.time()-t:.2f}s, {key.device_bytes()/1e6:.0f} MB on device", flush=True)
 d = circ.dims()
 w1 = circ.witness()
+if os.environ.get("ZKB_TUNE", "1") == "1":
+    print("windows before tune", key.windows(), flush=True)
+    key.tune(w1)
+    print(f"windows after tune {key.windows()}, {key.device_bytes()/1e6:.0f} MB on device", flush=True)
 ws = np.stack([w1] * batch)
 r = zkref.sha512_rng(5000, batch)
 s = zkref.sha512_rng(6000, batch)

@@ -71,6 +71,44 @@ def test_zklaim_batch_of_distinct_witnesses(zctx, ref, zklaim1):
         assert circ.verify(ws[i][: d["num_inputs"]], got[i])
 
 
+def test_key_tune_keeps_proofs_bit_exact(zctx, ref):
+    """zkb_key_tune re-plans the MSM windows from a sample witness: narrower windows for the 0 / 1-dominated
+    A / B queries, proofs unchanged (single proof, batch, and a dense witness under the tuned key)."""
+    circ = ref.Circuit.zklaim(1, 1)
+    circ.setup()
+    key = zctx.upload_key(circ.export_key())
+    d = circ.dims()
+    w = circ.witness()
+    before = key.windows()
+    key.tune(w)
+    after = key.windows()
+    assert after[0] < before[0] and after[1] < before[1] and after[3] < before[3], (before, after)
+    assert after[2] >= before[2] - 1  # the H query stays dense
+    _check_against_reference(zctx, ref, circ, key, w, 4242)
+    n = 3
+    ws = np.stack([ref.zklaim_witness(1, 900 + i, d["num_variables"]) for i in range(n)])
+    r = ref.sha512_rng(5100, n)
+    s = ref.sha512_rng(6100, n)
+    got = zctx.prove_batch(key, ws, r, s)
+    for i in range(n):
+        exp = circ.prove(ws[i], r[i], s[i], want_H=False)
+        assert ref.proof_bytes(got[i]) == ref.proof_bytes(exp["proof"]), i
+    key.tune(w)  # idempotent
+    assert key.windows() == after
+    key.free()
+    circ.free()
+
+
+def test_key_tune_dense_witness(zctx, ref):
+    circ = ref.Circuit.example(1013, 10, seed=5)
+    circ.setup()
+    key = zctx.upload_key(circ.export_key())
+    key.tune(circ.witness())
+    _check_against_reference(zctx, ref, circ, key, circ.witness(), 99)
+    key.free()
+    circ.free()
+
+
 def test_unsatisfied_witness_is_reported(zctx, ref, zklaim1):
     circ, key = zklaim1
     w = circ.witness().copy()

@@ -54,6 +54,8 @@ SYMBOLS = {
     "zkb_key_free": (None, [_vp]),
     "zkb_key_device_bytes": (_sz, [_vp]),
     "zkb_key_domain": (_i, [_vp, C.POINTER(_sz), C.POINTER(_i)]),
+    "zkb_key_tune": (_i, [_vp, _vp, _u64p]),
+    "zkb_key_windows": (_i, [_vp, C.POINTER(_i)]),
     "zkb_witness_map": (_i, [_vp, _vp, _u64p, _u64p]),
     "zkb_prove": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _vp, _u64p]),
     "zkb_prove_batch": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p, _vp]),
@@ -285,7 +287,7 @@ class Context:
         return np.frombuffer(out, dtype=np.uint64).reshape(count, 48).copy()
 
     # ---- measurement ------------------------------------------------------------------
-    def imad_peak(self, iters: int = 4096) -> float:
+    def imad_peak(self, iters: int = 512) -> float:
         return float(self.lib.zkb_measure_imad_peak(self.h, iters))
 
     def profile(self, enable: bool = True):
@@ -328,6 +330,20 @@ class Key:
 
     def device_bytes(self) -> int:
         return int(self.ctx.lib.zkb_key_device_bytes(self.h))
+
+    def tune(self, w) -> "Key":
+        """zkb_key_tune: re-plan the MSM windows for the 0 / 1 statistics of the sample witness w (proofs unchanged)."""
+        w = _arr(w, 4)
+        if w.shape[0] != self.num_variables:
+            raise ValueError("witness length != num_variables")
+        self.ctx._chk(self.ctx.lib.zkb_key_tune(self.ctx.h, self.h, w.ctypes.data))
+        return self
+
+    def windows(self):
+        """window bits planned for the A, B-in-G1, H + L and B-in-G2 queries"""
+        out = (C.c_int * 4)()
+        self.ctx._chk(self.ctx.lib.zkb_key_windows(self.h, out))
+        return list(out)
 
     def free(self):
         if self.h:

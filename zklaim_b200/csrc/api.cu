@@ -38,25 +38,47 @@ void prof_collect(zkb_ctx *ctx)
 using namespace zkb;
 
 namespace {
-// independent 64-bit multiply-add chains: 8 accumulators per thread, all lanes busy
-__global__ void k_imad_peak(uint64_t *out, int iters, uint32_t seed)
+// Integer multiply-add peak, measured with the instruction mix the whole library is made of: chains of Fq
+// Montgomery products (fp.cuh), each 128 IMAD.WIDE.U32(.X) + 8 IMAD = 136 multiply-adds of 32 x 32 (+ 64) bits.
+// Two independent chains per thread, 16 warps per SM sub-partition; every product depends on the previous one
+// of its chain, so ptxas can neither hoist nor strength-reduce anything (an earlier probe made of
+// mad.wide.u32 with loop-invariant operands was rewritten by ptxas into IADD3 chains and measured the ALU
+// pipe instead).  On B200 a warp-wide IMAD.WIDE occupies the fma-heavy pipe of its sub-partition for 4 cycles
+// (scripts/probe/pipe_probe.cu; profiles/r01_pipe_probe.txt), i.e. 32 wide multiply-adds per clock and SM:
+// 148 x 32 x 1.965 GHz = 9.31e12/s nominal; this kernel sustains ~97 % of that.
+__device__ __forceinline__ uint32_t mix32(uint32_t x)
 {
-    uint32_t a = seed + threadIdx.x, b = seed * 2654435761u + blockIdx.x;
-    uint64_t acc[8];
+    x ^= x >> 16;
+    x *= 0x7feb352du;
+    x ^= x >> 15;
+    x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
+}
+constexpr int IMAD_PER_MODMUL = 136;
+__global__ void __launch_bounds__(128) k_imad_peak(uint64_t *out, int iters, uint32_t seed)
+{
+    Fq a[2], b[2];
 #pragma unroll
-    for (int j = 0; j < 8; j++) acc[j] = (uint64_t)(j + 1) * a;
+    for (int c = 0; c < 2; c++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            a[c].v[j] = mix32(seed + threadIdx.x * 16 + j + 97 * c + blockIdx.x) >> (j == 7 ? 3 : 0);
+            b[c].v[j] = mix32(a[c].v[j] + 1) >> (j == 7 ? 3 : 0);
+        }
     for (int i = 0; i < iters; i++) {
 #pragma unroll
-        for (int j = 0; j < 8; j++)
-            asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[j]) : "r"(a + j), "r"(b));
-#pragma unroll
-        for (int j = 0; j < 8; j++)
-            asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[j]) : "r"(b + j), "r"(a));
+        for (int c = 0; c < 2; c++) {
+            a[c] = a[c] * b[c];
+            b[c] = b[c] * a[c];
+        }
     }
-    uint64_t s = 0;
+    uint32_t s = 0;
 #pragma unroll
-    for (int j = 0; j < 8; j++) s ^= acc[j];
-    if (s == 0x1234567ull) out[0] = s; // never true in practice; keeps the chains alive
+    for (int c = 0; c < 2; c++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) s ^= a[c].v[j] ^ b[c].v[j];
+    if (s == 0x1234567u) out[0] = s; // never true in practice; keeps the chains alive
 }
 } // namespace
 
@@ -79,11 +101,17 @@ int zkb_init(int device_id, zkb_ctx **out)
     ctx->dev = device_id;
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device_id) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+    if (cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->side_stream[0], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->side_stream[1], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_join[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_join[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
         delete ctx;
         return fail(nullptr, ZKB_ERR_CUDA, "zkb_init: stream/event creation failed");
     }
+    ctx->stream = ctx->main_stream;
     *out = ctx;
     return ZKB_OK;
 }
@@ -92,7 +120,7 @@ void zkb_shutdown(zkb_ctx *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->dev);
-    cudaStreamSynchronize(ctx->stream);
+    cudaDeviceSynchronize();
     for (auto &s : ctx->scratch) s.release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->prof_pairs_host) {
@@ -102,7 +130,12 @@ void zkb_shutdown(zkb_ctx *ctx)
     }
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
-    cudaStreamDestroy(ctx->stream);
+    cudaEventDestroy(ctx->ev_fork);
+    cudaEventDestroy(ctx->ev_join[0]);
+    cudaEventDestroy(ctx->ev_join[1]);
+    cudaStreamDestroy(ctx->main_stream);
+    cudaStreamDestroy(ctx->side_stream[0]);
+    cudaStreamDestroy(ctx->side_stream[1]);
     delete ctx;
 }
 
@@ -143,10 +176,10 @@ long zkb_last_kernel_launches(const zkb_ctx *ctx) { return ctx ? ctx->launches :
 double zkb_measure_imad_peak(zkb_ctx *ctx, int iters)
 {
     if (!ctx) return -1.0;
-    if (iters <= 0) iters = 4096;
+    if (iters <= 0) iters = 512;
     if (cudaSetDevice(ctx->dev) != cudaSuccess) return -1.0;
     if (ctx->scratch[SB_MISC].ensure(64) != cudaSuccess) return -1.0;
-    const int blocks = ctx->sm_count * 8, threads = 256;
+    const int blocks = ctx->sm_count * 16, threads = 128;
     double best = 0;
     for (int rep = 0; rep < 4; rep++) {
         cudaEventRecord(ctx->ev0, ctx->stream);
@@ -155,7 +188,7 @@ double zkb_measure_imad_peak(zkb_ctx *ctx, int iters)
         if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return -1.0;
         float ms = 0;
         cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
-        const double macs = (double)blocks * threads * (double)iters * 16.0;
+        const double macs = (double)blocks * threads * (double)iters * 4.0 * IMAD_PER_MODMUL;
         const double rate = macs / (ms * 1e-3);
         if (rep > 0 && rate > best) best = rate;
     }

@@ -41,7 +41,11 @@ struct DevBuf {
 struct zkb_ctx {
     int dev = 0;
     int sm_count = 148;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;          // the stream work is enqueued on right now (main unless a LaneScope is active)
+    cudaStream_t main_stream = nullptr;     // owns the timing events and every synchronisation with the host
+    cudaStream_t side_stream[2] = {nullptr, nullptr}; // prover: witness-only MSMs overlap the witness map
+    cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+    int lane_bias = 0;                      // scratch-slot offset of the active MSM lane
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
     double last_ms = 0.0;
@@ -61,14 +65,34 @@ struct zkb_ctx {
 
 namespace zkb {
 
-// scratch slots of a context (G1 and G2 pipelines own disjoint sets so that they may overlap)
+// scratch slots of a context.  An MSM run owns one "lane" of slots; the prover runs three lanes concurrently
+// (G1 job C on the main stream, G1 jobs A + B1 and the G2 job on the side streams)
 enum {
-    SB_HIST = 0, SB_START, SB_CURSOR, SB_BLOCKSUM, SB_ENT, SB_EBKT, SB_PARTS, SB_BUCKETS, SB_L1, SB_L2, SB_RES,
-    SB_PER_GROUP,                      // slots above are per group: index + group_slot(group)
-    SB_SCAL = 2 * SB_PER_GROUP, SB_PLAIN, SB_STAGE_A, SB_STAGE_B, SB_STAGE_O, SB_MISC,
+    SB_HIST = 0, SB_START, SB_CURSOR, SB_BLOCKSUM, SB_ENT, SB_EBKT, SB_PARTS, SB_BUCKETS, SB_L1, SB_L2, SB_RES, SB_WIDE,
+    SB_PER_GROUP,                      // slots above are per lane: index + msm_slot(ctx, group)
+    SB_SCAL = 3 * SB_PER_GROUP, SB_PLAIN, SB_STAGE_A, SB_STAGE_B, SB_STAGE_O, SB_MISC,
     SB_PROVER0 // first slot of prover.cu
 };
 inline int group_slot(int group) { return group == ZKB_G2 ? SB_PER_GROUP : 0; }
+inline int msm_slot(const zkb_ctx *ctx, int group) { return group_slot(group) + ctx->lane_bias; }
+constexpr int LANE_G1_SIDE = 2 * SB_PER_GROUP; // lane_bias of the second G1 lane
+
+// enqueue on a side stream / another scratch lane for the lifetime of the scope (host-side switch only)
+struct LaneScope {
+    zkb_ctx *ctx;
+    cudaStream_t saved_stream;
+    int saved_bias;
+    LaneScope(zkb_ctx *c, cudaStream_t st, int bias) : ctx(c), saved_stream(c->stream), saved_bias(c->lane_bias)
+    {
+        c->stream = st;
+        c->lane_bias = bias;
+    }
+    ~LaneScope()
+    {
+        ctx->stream = saved_stream;
+        ctx->lane_bias = saved_bias;
+    }
+};
 
 extern thread_local std::string g_init_err;
 

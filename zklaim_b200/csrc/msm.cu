@@ -234,7 +234,9 @@ int msm_choose_c(size_t n_eff, int group, int precompute_factor)
         int F = precompute_factor <= 0 ? W : precompute_factor;
         if (F > W) F = W;
         const int G = (W + F - 1) / F;
-        const double cost = (double)n_eff * W * madd + (double)G * (double)(1u << c) * add + (double)(G - 1) * c * dbl * 64;
+        // the bucket reduction runs at about half the arithmetic efficiency of the accumulation (scan overhead,
+        // short dependent chains): its additions are charged twice
+        const double cost = (double)n_eff * W * madd + 2.0 * G * (double)(1u << c) * add + (double)(G - 1) * c * dbl * 64;
         if (cost < best_cost) {
             best_cost = cost;
             best = c;
@@ -296,7 +298,7 @@ int msm_sort_pairs(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const u
                    int batch)
 {
     cudaStream_t st = ctx->stream;
-    const int gs = group_slot(plan->group);
+    const int gs = msm_slot(ctx, plan->group);
     size_t Emax = 0;
     for (uint32_t q = 0; q < tab.njobs; q++) Emax += (size_t)tab.j[q].n * tab.j[q].W;
     Emax *= (size_t)batch;
@@ -336,7 +338,7 @@ int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t
             XYZZ<F> *d_res)
 {
     typedef XYZZ<F> PT;
-    const int gs = group_slot(plan->group);
+    const int gs = msm_slot(ctx, plan->group);
     if (batch <= 0 || batch > 65535) return fail(ctx, ZKB_ERR_ARG, "msm: batch must be 1..65535");
     size_t Emax = 0;
     for (uint32_t q = 0; q < tab.njobs; q++) Emax += (size_t)tab.j[q].n * tab.j[q].W;
@@ -350,7 +352,7 @@ int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_BUCKETS].ensure(B * sizeof(PT)));
     if (runs) {
         const int g = plan->group == ZKB_G2 ? 1 : 0;
-        const bool prof = ctx->prof && !ctx->prof_pending[g]; // one sample per synchronisation
+        const bool prof = ctx->prof && !ctx->prof_pending[g] && (g == 1 || ctx->lane_bias == 0); // one sample per synchronisation
         if (prof) ZKB_CUDA(ctx, cudaEventRecord(ctx->pe[g][0], ctx->stream));
         rc = launch_accumulate<F>(ctx, (const Affine<F> *)plan->d_pts, ctx->scratch[gs + SB_ENT].as<uint32_t>(),
                                   ctx->scratch[gs + SB_EBKT].as<uint32_t>(), ctx->scratch[gs + SB_START].as<uint32_t>(),
@@ -364,7 +366,7 @@ int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t
             ctx->prof_pending[g] = true;
         }
     }
-    return msm_finish<F>(ctx, plan, tab, batch, S, d_res);
+    return msm_finish<F>(ctx, plan, tab, batch, S, runs, d_res);
 }
 
 int msm_to_plain(zkb_ctx *ctx, const void *d_mont, uint32_t *d_plain, size_t n)
@@ -440,7 +442,7 @@ int zkb_msm_device(zkb_ctx *ctx, const zkb_bases *bases, size_t offset, const vo
     tab.j[0].base_first = (uint32_t)offset;
     tab.j[0].scal_first = 0;
     tab.n_items = (uint32_t)n;
-    const int gs = group_slot(bases->plan.group);
+    const int gs = msm_slot(ctx, bases->plan.group);
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_RES].ensure(g1 ? sizeof(G1X) : sizeof(G2X)));
     if (g1) {
         rc = msm_run<Fq>(ctx, &bases->plan, tab, plain, 0, 1, ctx->scratch[gs + SB_RES].as<G1X>());

@@ -21,13 +21,14 @@ template <class PT> __device__ __forceinline__ PT sm_get(const uint32_t *sm, int
 }
 
 // merges the boundary partials of every bucket that spans more than one run; empty buckets -> infinity.
-// One lane per bucket for short spans; a bucket that spans many runs (the "scalar == 1" bucket of a
-// Groth16 witness holds thousands of pairs) is reduced by its whole warp.
-constexpr int FIXUP_T = 128, FIXUP_WIDE = 64;
+// One lane per bucket for short spans, the whole warp for medium spans; a bucket that spans very many runs
+// (the "scalar == 1" bucket of a Groth16 witness holds thousands of pairs) is queued for k_fixup_wide, where a
+// whole thread block reduces it.
+constexpr int FIXUP_T = 128, FIXUP_WARP = 8, FIXUP_BLOCK = 256;
 template <class F>
 __global__ void __launch_bounds__(FIXUP_T)
 k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__restrict__ buckets,
-        const XYZZ<F> *__restrict__ parts)
+        const XYZZ<F> *__restrict__ parts, uint32_t *__restrict__ wide_list)
 {
     extern __shared__ uint32_t sm[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -49,8 +50,10 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__r
             multi = t1 > t0;
         }
     }
-    const bool wide = multi && (t1 - t0) >= FIXUP_WIDE;
-    if (multi && !wide) {
+    const bool block_wide = multi && (t1 - t0) >= FIXUP_BLOCK;
+    const bool wide = multi && !block_wide && (t1 - t0) >= FIXUP_WARP;
+    if (block_wide) wide_list[1 + atomicAdd(wide_list, 1u)] = b;
+    if (multi && !wide && !block_wide) {
         XYZZ<F> acc = ld_vec(parts + 2 * (size_t)t0 + ((s == t0 * S) ? 0 : 1));
         for (uint32_t t = t0 + 1; t <= t1; t++) acc.add(ld_vec(parts + 2 * (size_t)t));
         st_vec(buckets + b, acc);
@@ -79,6 +82,38 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__r
         }
         if (lane == 0) st_vec(buckets + wb, acc);
         __syncwarp();
+    }
+}
+
+// the queued buckets, one thread block each (grid-stride over the queue)
+template <class F>
+__global__ void __launch_bounds__(FIXUP_T)
+k_fixup_wide(const uint32_t *__restrict__ start, uint32_t S, XYZZ<F> *__restrict__ buckets,
+             const XYZZ<F> *__restrict__ parts, const uint32_t *__restrict__ wide_list)
+{
+    extern __shared__ uint32_t sm[];
+    const int T = blockDim.x, t = threadIdx.x;
+    const uint32_t count = wide_list[0];
+    for (uint32_t i = blockIdx.x; i < count; i += gridDim.x) {
+        const uint32_t b = wide_list[1 + i];
+        const uint32_t s = start[b], e = start[b + 1];
+        const uint32_t t0 = s / S, t1 = (e - 1) / S;
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (uint32_t r = t0 + t; r <= t1; r += T) {
+            const size_t idx = (r == t0) ? 2 * (size_t)r + ((s == r * S) ? 0 : 1) : 2 * (size_t)r;
+            acc.add(ld_vec(parts + idx));
+        }
+        sm_put(sm, T, t, acc);
+        __syncthreads();
+        for (int d = T >> 1; d > 0; d >>= 1) {
+            if (t < d) {
+                acc.add(sm_get<XYZZ<F>>(sm, T, t + d));
+                sm_put(sm, T, t, acc);
+            }
+            __syncthreads();
+        }
+        if (t == 0) st_vec(buckets + b, acc);
+        __syncthreads();
     }
 }
 
@@ -223,24 +258,39 @@ k_next_copy(const Affine<F> *__restrict__ prev, Affine<F> *__restrict__ next, si
     st_vec(next + i, r);
 }
 
-template <class F> int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t S, XYZZ<F> *d_res)
+template <class F>
+int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t S, size_t ctx_runs_hint, XYZZ<F> *d_res)
 {
     typedef XYZZ<F> PT;
     cudaStream_t st = ctx->stream;
-    const int gs = group_slot(plan->group);
+    const int gs = msm_slot(ctx, plan->group);
     const size_t B = (size_t)tab.Bp * batch;
     uint32_t *start = ctx->scratch[gs + SB_START].as<uint32_t>();
     PT *parts = ctx->scratch[gs + SB_PARTS].as<PT>();
     PT *buckets = ctx->scratch[gs + SB_BUCKETS].as<PT>();
-    k_fixup<F><<<ceil_div(B, FIXUP_T), FIXUP_T, (FIXUP_T / 32) * 32 * sizeof(PT), st>>>(start, (uint32_t)B, S, buckets, parts);
+    // queue of buckets for the block-wide fix-up: a bucket enters it when it spans >= FIXUP_BLOCK runs
+    const size_t max_wide = (size_t)((uint64_t)ctx_runs_hint / FIXUP_BLOCK) + 1;
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_WIDE].ensure((max_wide + 1) * 4));
+    uint32_t *wide = ctx->scratch[gs + SB_WIDE].as<uint32_t>();
+    ZKB_CUDA(ctx, cudaMemsetAsync(wide, 0, 4, st));
+    k_fixup<F><<<ceil_div(B, FIXUP_T), FIXUP_T, (FIXUP_T / 32) * 32 * sizeof(PT), st>>>(start, (uint32_t)B, S, buckets, parts, wide);
     ZKB_LAUNCH_CHECK(ctx);
+    {
+        size_t wblocks = max_wide < (size_t)ctx->sm_count * 2 ? max_wide : (size_t)ctx->sm_count * 2;
+        k_fixup_wide<F><<<(unsigned)wblocks, FIXUP_T, FIXUP_T * sizeof(PT), st>>>(start, S, buckets, parts, wide);
+        ZKB_LAUNCH_CHECK(ctx);
+    }
     for (uint32_t q = 0; q < tab.njobs; q++) {
         const MsmJob &J = tab.j[q];
         const uint32_t nb = 1u << (J.c - 1);
         // level-1 reduction geometry: nb = NB * T * L
+        // buckets per thread: enough threads to fill the device when the batch is small (the serial chain is
+        // 2 L + 2 log2 T additions deep), fewer scan steps per bucket when there is plenty of work
         const int T = (int)(nb < 128 ? nb : 128);
-        int L = (int)(nb / T);
-        if (L > 8) L = 8;
+        const size_t all_buckets = (size_t)nb * J.G * batch;
+        int L = 1;
+        while (L < 8 && L < (int)(nb / T) && all_buckets / (2 * L) >= (size_t)ctx->sm_count * 1024) L <<= 1;
+        while (nb / ((uint32_t)T * L) > 128) L <<= 1; // level 2 handles at most 128 level-1 blocks per set
         const int NB = (int)(nb / ((uint32_t)T * L));
         if (NB > 128) return fail(ctx, ZKB_ERR_ARG, "msm: window too wide for the bucket reduction");
         int T2 = 1;
@@ -286,13 +336,15 @@ template <class F> int results_to_host(zkb_ctx *ctx, const XYZZ<F> *d_res, size_
     return ZKB_OK;
 }
 
-// uploads the bases of one job (copy 0) and derives the other copies on the device (asynchronous on the stream)
-template <class F> int plan_upload_job(zkb_ctx *ctx, MsmPlan *plan, int job, const uint64_t *affine_host)
+// installs the bases of one job: copy 0 from `affine` (host memory, or device memory when `from_device`), the other
+// copies derived on the device (asynchronous on the stream)
+template <class F> int plan_upload_job(zkb_ctx *ctx, MsmPlan *plan, int job, const uint64_t *affine, bool from_device)
 {
     const MsmJob &J = plan->tab.j[job];
     const size_t n = J.n_total;
     Affine<F> *p = (Affine<F> *)plan->d_pts + J.pts_off;
-    ZKB_CUDA(ctx, cudaMemcpyAsync(p, affine_host, n * sizeof(Affine<F>), cudaMemcpyHostToDevice, ctx->stream));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(p, affine, n * sizeof(Affine<F>), from_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                                  ctx->stream));
     for (int q = 1; q < J.F; q++) {
         k_next_copy<F><<<ceil_div(n, 128), 128, 0, ctx->stream>>>(p + (size_t)(q - 1) * n, p + (size_t)q * n, n, J.G * J.c);
         ZKB_LAUNCH_CHECK(ctx);

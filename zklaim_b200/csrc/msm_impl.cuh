@@ -56,8 +56,9 @@ int launch_accumulate(zkb_ctx *ctx, const Affine<F> *pts, const uint32_t *ent, c
                       const uint32_t *start, uint32_t B, uint32_t S, XYZZ<F> *buckets, XYZZ<F> *parts, size_t runs);
 
 // msm_g1.cu / msm_g2.cu: fix-up, bucket reduction, per-job result (XYZZ, device, [batch][njobs]); base precomputation
-template <class F> int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t S, XYZZ<F> *d_res);
-template <class F> int plan_upload_job(zkb_ctx *ctx, MsmPlan *plan, int job, const uint64_t *affine_host);
+template <class F>
+int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t S, size_t runs, XYZZ<F> *d_res);
+template <class F> int plan_upload_job(zkb_ctx *ctx, MsmPlan *plan, int job, const uint64_t *affine, bool from_device = false);
 template <class F> int results_to_host(zkb_ctx *ctx, const XYZZ<F> *d_res, size_t count, uint64_t *out_jacobian);
 
 // the whole pipeline: plain scalars (device, `zstride` words between proofs) -> d_res[batch][njobs]

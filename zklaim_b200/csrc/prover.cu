@@ -13,13 +13,18 @@
 //      constraints, r1cs_to_qap.tcc:228-238, :277-283) plus the satisfiability check;
 //   2. iFFT + cosetFFT of the 3 * batch vectors (ntt.cu), H = (A B - C) / Z on the coset,
 //      icosetFFT -> H coefficients written straight into Z and P;
-//   3. one G1 MSM run with three jobs and one G2 run with one job (msm.cu).  The fixed key
-//      elements ride along as extra bases so that no variable-time work is left for them:
-//        job A  = A_query + {alpha_g1 (scalar 1), delta_g1 (scalar r)}      = g1_A  (tcc:488)
-//        job B1 = B_query.h + {beta_g1 (1), delta_g1 (s)}                     = g1_B  (tcc:491)
-//        job C  = H_query + L_query + {delta_g1 (-rs)}                        = Ht + Lt - rs delta
-//        job B2 = B_query.g + {beta_g2 (1), delta_g2 (s)}                     = g2_B  (tcc:492)
-//   4. assembly: g1_C = job C + s g1_A + r g1_B  (tcc:495), two scalar multiplications per proof.
+//   3. three MSM runs (msm.cu).  The fixed key elements ride along as extra bases so that no variable-time
+//      work is left for them:
+//        run G1ab: job A  = A_query + {alpha_g1 (scalar 1), delta_g1 (scalar r)}      = g1_A  (tcc:488)
+//                  job B1 = B_query.h + {beta_g1 (1), delta_g1 (s)}                     = g1_B  (tcc:491)
+//        run G2:   job B2 = B_query.g + {beta_g2 (1), delta_g2 (s)}                     = g2_B  (tcc:492)
+//        run G1c:  job C  = H_query + L_query + {delta_g1 (-rs)}                        = Ht + Lt - rs delta
+//      G1ab and G2 need only the witness: they run on two side streams, concurrently with stages 1-2 and
+//      with G1c (which needs H) on the main stream; so do the two scalar multiplications s g1_A, r g1_B;
+//   4. assembly: g1_C = job C + s g1_A + r g1_B  (tcc:495).
+//
+// zkb_key_tune() re-plans the window widths of the witness-driven jobs from the scalar statistics of a sample
+// witness (the reference special-cases 0 / 1 scalars for the same reason, multiexp.tcc:466-481).
 #define ZKB_NOINLINE_MUL 1
 #include "msm_impl.cuh"
 #include "ntt.cuh"
@@ -36,7 +41,9 @@ struct zkb_key {
     uint32_t *col[3] = {nullptr, nullptr, nullptr};
     Fr *coeff[3] = {nullptr, nullptr, nullptr};
     size_t nnz[3] = {0, 0, 0};
-    MsmPlan g1, g2;
+    MsmPlan g1ab, g1c, g2;              // see the header: jobs {A, B1}, {C}, {B2}
+    std::vector<uint32_t> h_sidx[3];    // host copies of the scalar maps (g1ab, g1c, g2), for zkb_key_tune
+    size_t nnzB = 0;
     size_t zlen = 0; // elements per row of Z
     size_t bytes = 0;
     // offsets into a row of Z
@@ -49,7 +56,7 @@ struct zkb_key {
 
 namespace {
 
-enum { SP_Z = SB_PROVER0, SP_P, SP_ABC, SP_TMP, SP_RS, SP_FLAGS, SP_PROOF, SP_W, SP_RES1, SP_RES2 };
+enum { SP_Z = SB_PROVER0, SP_P, SP_ABC, SP_TMP, SP_RS, SP_FLAGS, SP_PROOF, SP_W, SP_RES_AB, SP_RES_C, SP_RES2, SP_SMUL };
 
 struct CsrDev {
     const uint32_t *rowptr[3];
@@ -137,30 +144,49 @@ __global__ void k_z_plain(const Fr *__restrict__ Z, Fr *__restrict__ P, size_t z
     st_vec(P + o, ld_vec(Z + o).from_mont());
 }
 
+// sm[2p] = s * g1_A, sm[2p + 1] = r * g1_B: the two variable-base scalar multiplications of
+// r1cs_gg_ppzksnark.tcc:495.  One warp each (a lone lane costs what a full warp costs; the chain of
+// doublings is serial): 4-bit fixed windows, the 15 multiples tabulated in shared memory.
+__global__ void __launch_bounds__(64)
+k_smul(const G1X *__restrict__ rab, const Fr *__restrict__ P, size_t zlen, size_t nv, G1X *__restrict__ sm)
+{
+    __shared__ G1X tab[2][16];
+    const int p = blockIdx.x, which = threadIdx.x >> 5; // 0: s * g1_A, 1: r * g1_B
+    if (threadIdx.x & 31) return;
+    const Fr k = ld_vec(P + (size_t)p * zlen + (which == 0 ? nv + 2 : nv + 1));
+    G1X *T = tab[which];
+    const G1X base = ld_vec(rab + 2 * (size_t)p + which);
+    T[0] = G1X::inf();
+    T[1] = base;
+    for (int d = 2; d < 16; d++) {
+        G1X v = T[d >> 1];
+        v = v.dbl();
+        if (d & 1) v.add(base);
+        T[d] = v;
+    }
+    G1X acc = G1X::inf();
+    for (int w = 63; w >= 0; w--) {
+        if (w != 63)
+            for (int i = 0; i < 4; i++) acc = acc.dbl();
+        const uint32_t d = (k.v[w >> 3] >> ((w & 7) * 4)) & 15u;
+        if (d) acc.add(T[d]);
+    }
+    st_vec(sm + 2 * (size_t)p + which, acc);
+}
+
 // g1_C = job C + s * g1_A + r * g1_B (r1cs_gg_ppzksnark.tcc:495); proof = (g1_A, g2_B, g1_C) as Jacobian limbs
 __global__ void __launch_bounds__(64)
-k_assemble(const G1X *__restrict__ r1, const G2X *__restrict__ r2, const Fr *__restrict__ P, size_t zlen, size_t nv,
-           zkb_proof *__restrict__ out)
+k_assemble(const G1X *__restrict__ rab, const G1X *__restrict__ rc, const G1X *__restrict__ sm, const G2X *__restrict__ r2,
+           int batch, zkb_proof *__restrict__ out)
 {
-    __shared__ G1X sh[2];
-    const int p = blockIdx.x;
-    const Fr *pl = P + (size_t)p * zlen;
-    const int t = threadIdx.x;
-    if (t == 0 || t == 32) {
-        const int which = t >> 5; // 0: s * g1_A, 1: r * g1_B
-        const Fr k = ld_vec(pl + (which == 0 ? nv + 2 : nv + 1));
-        sh[which] = scalar_mul<Fq>(k.v, ld_vec(r1 + 3 * (size_t)p + which));
-    }
-    __syncthreads();
-    if (t == 0) {
-        G1X c = ld_vec(r1 + 3 * (size_t)p + 2);
-        c.add(sh[0]);
-        c.add(sh[1]);
-        const G1J A = ld_vec(r1 + 3 * (size_t)p).to_jacobian(), C = c.to_jacobian();
-        st_vec(reinterpret_cast<G1J *>(out[p].A), A);
-        st_vec(reinterpret_cast<G1J *>(out[p].C), C);
-    }
-    if (t == 32) st_vec(reinterpret_cast<G2J *>(out[p].B), ld_vec(r2 + p).to_jacobian());
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= batch) return;
+    G1X c = ld_vec(rc + p);
+    c.add(ld_vec(sm + 2 * (size_t)p));
+    c.add(ld_vec(sm + 2 * (size_t)p + 1));
+    st_vec(reinterpret_cast<G1J *>(out[p].A), ld_vec(rab + 2 * (size_t)p).to_jacobian());
+    st_vec(reinterpret_cast<G1J *>(out[p].C), c.to_jacobian());
+    st_vec(reinterpret_cast<G2J *>(out[p].B), ld_vec(r2 + p).to_jacobian());
 }
 
 } // namespace
@@ -205,7 +231,8 @@ void key_release(zkb_key *key)
         if (key->col[k]) cudaFree(key->col[k]);
         if (key->coeff[k]) cudaFree(key->coeff[k]);
     }
-    plan_free(&key->g1);
+    plan_free(&key->g1ab);
+    plan_free(&key->g1c);
     plan_free(&key->g2);
     domain_free(&key->dom);
     delete key;
@@ -234,70 +261,98 @@ int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key)
     for (int k = 0; k < 3; k++)
         if ((rc = upload_csr(ctx, key, k, *mats[k]))) return rc;
     key->zlen = (nv + 4 + m + 1 + 3) & ~(size_t)3;
+    key->nnzB = d->B_nnz;
 
-    // ---- G1 plan: jobs A, B1, C ----
+    // ---- MSM plans: {A, B1}, {C} in G1 and {B2} in G2 ----
     const size_t nA = nv + 3, nB = d->B_nnz + 2, nL = nv - ni, nC = (m - 1) + nL + 1;
-    key->g1.group = ZKB_G1;
+    key->g1ab.group = ZKB_G1;
+    key->g1c.group = ZKB_G1;
     key->g2.group = ZKB_G2;
     // witness-driven queries are mostly 0 / 1 scalars in practice (r1cs_gg_ppzksnark.tcc:442-485 uses the
-    // mixed-addition variants for them); H is dense
-    if ((rc = plan_add_job(ctx, &key->g1, nA, msm_choose_c(nA / 4 + 1, ZKB_G1, 0), 0))) return rc;
-    if ((rc = plan_add_job(ctx, &key->g1, nB, msm_choose_c(nB / 4 + 1, ZKB_G1, 0), 0))) return rc;
-    if ((rc = plan_add_job(ctx, &key->g1, nC, msm_choose_c((m - 1) + nL / 4 + 1, ZKB_G1, 0), 0))) return rc;
+    // mixed-addition variants for them); H is dense.  zkb_key_tune refines the guess from a real witness.
+    if ((rc = plan_add_job(ctx, &key->g1ab, nA, msm_choose_c(nA / 4 + 1, ZKB_G1, 0), 0))) return rc;
+    if ((rc = plan_add_job(ctx, &key->g1ab, nB, msm_choose_c(nB / 4 + 1, ZKB_G1, 0), 0))) return rc;
+    if ((rc = plan_add_job(ctx, &key->g1c, nC, msm_choose_c((m - 1) + nL / 4 + 1, ZKB_G1, 0), 0))) return rc;
     if ((rc = plan_add_job(ctx, &key->g2, nB, msm_choose_c(nB / 4 + 1, ZKB_G2, 0), 0))) return rc;
-    if ((rc = plan_alloc(ctx, &key->g1))) return rc;
+    if ((rc = plan_alloc(ctx, &key->g1ab))) return rc;
+    if ((rc = plan_alloc(ctx, &key->g1c))) return rc;
     if ((rc = plan_alloc(ctx, &key->g2))) return rc;
-    key->bytes += key->g1.bytes + key->g2.bytes;
 
     std::vector<uint64_t> st;
-    std::vector<uint32_t> sidx1, sidx2;
-    sidx1.reserve(nA + nB + nC);
-    // job A
+    std::vector<uint32_t> &sab = key->h_sidx[0], &sc = key->h_sidx[1], &s2 = key->h_sidx[2];
+    sab.reserve(nA + nB);
     st.reserve(nC * 8);
+    // job A
     append_pts(st, d->A_query, nv + 1, 8);
     append_pts(st, d->alpha_g1, 1, 8);
     append_pts(st, d->delta_g1, 1, 8);
-    for (size_t i = 0; i <= nv; i++) sidx1.push_back((uint32_t)i);
-    sidx1.push_back(0);
-    sidx1.push_back((uint32_t)key->z_r());
-    if ((rc = plan_upload_job<Fq>(ctx, &key->g1, 0, st.data()))) return rc;
+    for (size_t i = 0; i <= nv; i++) sab.push_back((uint32_t)i);
+    sab.push_back(0);
+    sab.push_back((uint32_t)key->z_r());
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1ab, 0, st.data()))) return rc;
     ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     // job B1
     st.clear();
     append_pts(st, d->B_g1, d->B_nnz, 8);
     append_pts(st, d->beta_g1, 1, 8);
     append_pts(st, d->delta_g1, 1, 8);
-    for (size_t k = 0; k < d->B_nnz; k++) sidx1.push_back(d->B_index[k]);
-    sidx1.push_back(0);
-    sidx1.push_back((uint32_t)key->z_s());
-    if ((rc = plan_upload_job<Fq>(ctx, &key->g1, 1, st.data()))) return rc;
+    for (size_t k = 0; k < d->B_nnz; k++) sab.push_back(d->B_index[k]);
+    sab.push_back(0);
+    sab.push_back((uint32_t)key->z_s());
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1ab, 1, st.data()))) return rc;
     ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     // job C
     st.clear();
     append_pts(st, d->H_query, m - 1, 8);
     append_pts(st, d->L_query, nL, 8);
     append_pts(st, d->delta_g1, 1, 8);
-    for (size_t j = 0; j + 1 < m; j++) sidx1.push_back((uint32_t)(key->z_h() + j));
-    for (size_t j = 0; j < nL; j++) sidx1.push_back((uint32_t)(1 + ni + j));
-    sidx1.push_back((uint32_t)key->z_nrs());
-    if ((rc = plan_upload_job<Fq>(ctx, &key->g1, 2, st.data()))) return rc;
+    for (size_t j = 0; j + 1 < m; j++) sc.push_back((uint32_t)(key->z_h() + j));
+    for (size_t j = 0; j < nL; j++) sc.push_back((uint32_t)(1 + ni + j));
+    sc.push_back((uint32_t)key->z_nrs());
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1c, 0, st.data()))) return rc;
     ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     // job B2
     st.clear();
     append_pts(st, d->B_g2, d->B_nnz, 16);
     append_pts(st, d->beta_g2, 1, 16);
     append_pts(st, d->delta_g2, 1, 16);
-    for (size_t k = 0; k < d->B_nnz; k++) sidx2.push_back(d->B_index[k]);
-    sidx2.push_back(0);
-    sidx2.push_back((uint32_t)key->z_s());
+    for (size_t k = 0; k < d->B_nnz; k++) s2.push_back(d->B_index[k]);
+    s2.push_back(0);
+    s2.push_back((uint32_t)key->z_s());
     if ((rc = plan_upload_job<Fq2>(ctx, &key->g2, 0, st.data()))) return rc;
     ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 
-    ZKB_CUDA(ctx, cudaMalloc(&key->g1.d_sidx, sidx1.size() * 4));
-    ZKB_CUDA(ctx, cudaMalloc(&key->g2.d_sidx, sidx2.size() * 4));
-    ZKB_CUDA(ctx, cudaMemcpy(key->g1.d_sidx, sidx1.data(), sidx1.size() * 4, cudaMemcpyHostToDevice));
-    ZKB_CUDA(ctx, cudaMemcpy(key->g2.d_sidx, sidx2.size() ? sidx2.data() : nullptr, sidx2.size() * 4, cudaMemcpyHostToDevice));
-    key->bytes += (sidx1.size() + sidx2.size()) * 4;
+    MsmPlan *plans[3] = {&key->g1ab, &key->g1c, &key->g2};
+    for (int k = 0; k < 3; k++) {
+        const std::vector<uint32_t> &v = key->h_sidx[k];
+        ZKB_CUDA(ctx, cudaMalloc(&plans[k]->d_sidx, v.size() * 4 + 4));
+        ZKB_CUDA(ctx, cudaMemcpy(plans[k]->d_sidx, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+        key->bytes += plans[k]->bytes + v.size() * 4;
+    }
+    return ZKB_OK;
+}
+
+// rebuilds `plan` with the window widths `c[job]`: copy 0 of every job is taken from the old plan on the device
+template <class F> int replan(zkb_ctx *ctx, MsmPlan *plan, const int *c)
+{
+    MsmPlan np;
+    np.group = plan->group;
+    int rc;
+    for (uint32_t q = 0; q < plan->tab.njobs; q++)
+        if ((rc = plan_add_job(ctx, &np, plan->tab.j[q].n_total, c[q], 0))) return rc;
+    if ((rc = plan_alloc(ctx, &np))) return rc;
+    for (uint32_t q = 0; q < plan->tab.njobs; q++) {
+        const uint64_t *src = (const uint64_t *)((const Affine<F> *)plan->d_pts + plan->tab.j[q].pts_off);
+        if ((rc = plan_upload_job<F>(ctx, &np, (int)q, src, true))) {
+            plan_free(&np);
+            return rc;
+        }
+    }
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    np.d_sidx = plan->d_sidx;
+    plan->d_sidx = nullptr;
+    plan_free(plan);
+    *plan = np;
     return ZKB_OK;
 }
 
@@ -311,14 +366,16 @@ size_t pairs_per_proof(const MsmPlan &pl)
 // proofs per chunk: bounded by the 2^32 pair-list positions of one MSM run and a scratch-memory budget
 int chunk_size(const zkb_key *key, size_t count)
 {
-    const size_t e1 = pairs_per_proof(key->g1), e2 = pairs_per_proof(key->g2);
-    const size_t per_proof = e1 * 8 + e1 / 4 * 16 + (size_t)key->g1.tab.Bp * 132 + e2 * 8 + e2 / 4 * 32 +
-                             (size_t)key->g2.tab.Bp * 260 + key->m * 32 * 6 + key->zlen * 64;
+    const size_t eab = pairs_per_proof(key->g1ab), ec = pairs_per_proof(key->g1c), e2 = pairs_per_proof(key->g2);
+    const size_t e1 = eab > ec ? eab : ec;
+    const size_t b1 = key->g1ab.tab.Bp > key->g1c.tab.Bp ? key->g1ab.tab.Bp : key->g1c.tab.Bp;
+    const size_t per_proof = (eab + ec) * 8 + (eab + ec) / 4 * 16 + ((size_t)key->g1ab.tab.Bp + key->g1c.tab.Bp) * 132 + e2 * 8 +
+                             e2 / 4 * 32 + (size_t)key->g2.tab.Bp * 260 + key->m * 32 * 6 + key->zlen * 64;
     size_t c = 64;
     const size_t budget = (size_t)32 << 30;
     if (c > budget / per_proof) c = budget / per_proof;
     if (c > ((1ull << 31) / (e1 + 1))) c = (1ull << 31) / (e1 + 1);
-    if (c > ((1ull << 31) / ((size_t)key->g1.tab.Bp + 1))) c = (1ull << 31) / ((size_t)key->g1.tab.Bp + 1);
+    if (c > ((1ull << 31) / (b1 + 1))) c = (1ull << 31) / (b1 + 1);
     if (c > count) c = count;
     return c ? (int)c : 1;
 }
@@ -369,17 +426,47 @@ int stage_rows(zkb_ctx *ctx, const zkb_key *key, int batch, const Fr *d_rs, uint
     return ZKB_OK;
 }
 
-int msm_and_assemble(zkb_ctx *ctx, const zkb_key *key, int batch, zkb_proof *d_out)
+// the witness-only MSM runs and the two scalar multiplications, on the side streams (forked after stage_rows)
+int msm_side_lanes(zkb_ctx *ctx, const zkb_key *key, int batch)
 {
     const uint32_t *P = ctx->scratch[SP_P].as<uint32_t>();
-    ZKB_CUDA(ctx, ctx->scratch[SP_RES1].ensure((size_t)3 * batch * sizeof(G1X)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_RES_AB].ensure((size_t)2 * batch * sizeof(G1X)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_SMUL].ensure((size_t)2 * batch * sizeof(G1X)));
     ZKB_CUDA(ctx, ctx->scratch[SP_RES2].ensure((size_t)batch * sizeof(G2X)));
-    G1X *r1 = ctx->scratch[SP_RES1].as<G1X>();
+    G1X *rab = ctx->scratch[SP_RES_AB].as<G1X>(), *sm = ctx->scratch[SP_SMUL].as<G1X>();
     G2X *r2 = ctx->scratch[SP_RES2].as<G2X>();
-    int rc = msm_run<Fq>(ctx, &key->g1, key->g1.tab, P, key->zlen * 8, batch, r1);
-    if (!rc) rc = msm_run<Fq2>(ctx, &key->g2, key->g2.tab, P, key->zlen * 8, batch, r2);
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->main_stream));
+    {
+        LaneScope lane(ctx, ctx->side_stream[0], LANE_G1_SIDE);
+        ZKB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_fork, 0));
+        int rc = msm_run<Fq>(ctx, &key->g1ab, key->g1ab.tab, P, key->zlen * 8, batch, rab);
+        if (rc) return rc;
+        k_smul<<<batch, 64, 0, ctx->stream>>>(rab, ctx->scratch[SP_P].as<Fr>(), key->zlen, key->nv, sm);
+        ZKB_LAUNCH_CHECK(ctx);
+        ZKB_CUDA(ctx, cudaEventRecord(ctx->ev_join[0], ctx->stream));
+    }
+    {
+        LaneScope lane(ctx, ctx->side_stream[1], 0);
+        ZKB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_fork, 0));
+        int rc = msm_run<Fq2>(ctx, &key->g2, key->g2.tab, P, key->zlen * 8, batch, r2);
+        if (rc) return rc;
+        ZKB_CUDA(ctx, cudaEventRecord(ctx->ev_join[1], ctx->stream));
+    }
+    return ZKB_OK;
+}
+
+// job C (needs H) on the main stream, then the join with the side lanes and the assembly
+int msm_main_lane_and_assemble(zkb_ctx *ctx, const zkb_key *key, int batch, zkb_proof *d_out)
+{
+    const uint32_t *P = ctx->scratch[SP_P].as<uint32_t>();
+    ZKB_CUDA(ctx, ctx->scratch[SP_RES_C].ensure((size_t)batch * sizeof(G1X)));
+    G1X *rc_ = ctx->scratch[SP_RES_C].as<G1X>();
+    int rc = msm_run<Fq>(ctx, &key->g1c, key->g1c.tab, P, key->zlen * 8, batch, rc_);
     if (rc) return rc;
-    k_assemble<<<batch, 64, 0, ctx->stream>>>(r1, r2, ctx->scratch[SP_P].as<Fr>(), key->zlen, key->nv, d_out);
+    ZKB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[0], 0));
+    ZKB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[1], 0));
+    k_assemble<<<ceil_div((size_t)batch, 64), 64, 0, ctx->stream>>>(ctx->scratch[SP_RES_AB].as<G1X>(), rc_, ctx->scratch[SP_SMUL].as<G1X>(),
+                                                                  ctx->scratch[SP_RES2].as<G2X>(), batch, d_out);
     ZKB_LAUNCH_CHECK(ctx);
     return ZKB_OK;
 }
@@ -423,9 +510,13 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
         }
         ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
         int rc = stage_rows(ctx, key, batch, rs, flags);
+        if (!rc && !map_only) rc = msm_side_lanes(ctx, key, batch);
         if (!rc) rc = witness_map_chunk(ctx, key, batch, flags);
-        if (!rc && !map_only) rc = msm_and_assemble(ctx, key, batch, d_out);
-        if (rc) return rc;
+        if (!rc && !map_only) rc = msm_main_lane_and_assemble(ctx, key, batch, d_out);
+        if (rc) {
+            cudaDeviceSynchronize(); // never leave a side stream running behind an error return
+            return rc;
+        }
         ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
         const size_t pin_bytes = (size_t)batch * (sizeof(zkb_proof) + 4);
         if (ensure_pinned(ctx, pin_bytes)) return ZKB_ERR_CUDA;
@@ -467,6 +558,54 @@ int zkb_key_upload(zkb_ctx *ctx, const zkb_key_desc *desc, zkb_key **out)
         return rc;
     }
     *out = key;
+    return ZKB_OK;
+}
+
+int zkb_key_tune(zkb_ctx *ctx, zkb_key *key, const uint64_t *w)
+{
+    if (!ctx || !key || !w) return fail(ctx, ZKB_ERR_ARG, "zkb_key_tune: bad argument");
+    if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_key_tune: key lives on another device");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    ZKB_CUDA(ctx, cudaDeviceSynchronize());
+    static const uint64_t one_r[4] = {0xac96341c4ffffffbull, 0x36fc76959f60cd29ull, 0x666ea36f7879462eull, 0x0e0a77c19a07df2full};
+    const size_t nv = key->nv;
+    // is the scalar at index si of a row of Z neither 0 nor 1?  (0 = the constant, 1..nv = w, above = r, s, -rs, H: dense)
+    auto dense = [&](uint32_t si) -> bool {
+        if (si == 0) return false;
+        if (si > nv) return true;
+        const uint64_t *x = w + 4 * (size_t)(si - 1);
+        if ((x[0] | x[1] | x[2] | x[3]) == 0) return false;
+        return memcmp(x, one_r, 32) != 0;
+    };
+    MsmPlan *plans[3] = {&key->g1ab, &key->g1c, &key->g2};
+    for (int k = 0; k < 3; k++) {
+        MsmPlan *pl = plans[k];
+        int c[MSM_MAX_JOBS];
+        bool changed = false;
+        for (uint32_t q = 0; q < pl->tab.njobs; q++) {
+            const MsmJob &J = pl->tab.j[q];
+            size_t nd = 0;
+            for (uint32_t i = 0; i < J.n_total; i++) nd += dense(key->h_sidx[k][J.item_begin + i]) ? 1 : 0;
+            c[q] = msm_choose_c(nd + 1, pl->group, 0);
+            if (c[q] < 7) c[q] = 7; // at most 37 precomputed copies of the bases
+            changed |= c[q] != J.c;
+        }
+        if (!changed) continue;
+        key->bytes -= pl->bytes;
+        const int rc = pl->group == ZKB_G1 ? replan<Fq>(ctx, pl, c) : replan<Fq2>(ctx, pl, c);
+        key->bytes += pl->bytes;
+        if (rc) return rc;
+    }
+    return ZKB_OK;
+}
+
+int zkb_key_windows(const zkb_key *key, int out[4])
+{
+    if (!key || !out) return ZKB_ERR_ARG;
+    out[0] = key->g1ab.tab.j[0].c;
+    out[1] = key->g1ab.tab.j[1].c;
+    out[2] = key->g1c.tab.j[0].c;
+    out[3] = key->g2.tab.j[0].c;
     return ZKB_OK;
 }
 
