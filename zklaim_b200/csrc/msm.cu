@@ -340,24 +340,19 @@ int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t
     typedef XYZZ<F> PT;
     const int gs = msm_slot(ctx, plan->group);
     if (batch <= 0 || batch > 65535) return fail(ctx, ZKB_ERR_ARG, "msm: batch must be 1..65535");
-    size_t Emax = 0;
-    for (uint32_t q = 0; q < tab.njobs; q++) Emax += (size_t)tab.j[q].n * tab.j[q].W;
-    Emax *= (size_t)batch;
     const size_t B = (size_t)tab.Bp * batch;
-    const uint32_t S = msm_run_length(ctx, Emax);
-    const size_t runs = (Emax + S - 1) / S;
+    const uint32_t rmax = msm_max_runs(ctx);
     int rc = msm_sort_pairs(ctx, plan, tab, d_plain, zstride, batch);
     if (rc) return rc;
-    ZKB_CUDA(ctx, ctx->scratch[gs + SB_PARTS].ensure(2 * (runs + 1) * sizeof(PT)));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_PARTS].ensure(2 * ((size_t)rmax + 1) * sizeof(PT)));
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_BUCKETS].ensure(B * sizeof(PT)));
-    if (runs) {
+    {
         const int g = plan->group == ZKB_G2 ? 1 : 0;
         const bool prof = ctx->prof && !ctx->prof_pending[g] && (g == 1 || ctx->lane_bias == 0); // one sample per synchronisation
         if (prof) ZKB_CUDA(ctx, cudaEventRecord(ctx->pe[g][0], ctx->stream));
         rc = launch_accumulate<F>(ctx, (const Affine<F> *)plan->d_pts, ctx->scratch[gs + SB_ENT].as<uint32_t>(),
                                   ctx->scratch[gs + SB_EBKT].as<uint32_t>(), ctx->scratch[gs + SB_START].as<uint32_t>(),
-                                  (uint32_t)B, S, ctx->scratch[gs + SB_BUCKETS].as<PT>(),
-                                  ctx->scratch[gs + SB_PARTS].as<PT>(), runs);
+                                  (uint32_t)B, rmax, ctx->scratch[gs + SB_BUCKETS].as<PT>(), ctx->scratch[gs + SB_PARTS].as<PT>());
         if (rc) return rc;
         if (prof) {
             ZKB_CUDA(ctx, cudaEventRecord(ctx->pe[g][1], ctx->stream));
@@ -366,7 +361,7 @@ int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t
             ctx->prof_pending[g] = true;
         }
     }
-    return msm_finish<F>(ctx, plan, tab, batch, S, runs, d_res);
+    return msm_finish<F>(ctx, plan, tab, batch, rmax, d_res);
 }
 
 int msm_to_plain(zkb_ctx *ctx, const void *d_mont, uint32_t *d_plain, size_t n)

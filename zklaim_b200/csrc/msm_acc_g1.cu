@@ -3,5 +3,5 @@
 #include "msm_acc_impl.cuh"
 namespace zkb {
 template int launch_accumulate<Fq>(zkb_ctx *, const Affine<Fq> *, const uint32_t *, const uint32_t *, const uint32_t *,
-                                   uint32_t, uint32_t, XYZZ<Fq> *, XYZZ<Fq> *, size_t);
+                                   uint32_t, uint32_t, XYZZ<Fq> *, XYZZ<Fq> *);
 }

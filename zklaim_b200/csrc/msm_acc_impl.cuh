@@ -10,11 +10,12 @@ namespace zkb {
 template <class F>
 __global__ void __launch_bounds__(128)
 k_accumulate(const Affine<F> *__restrict__ pts, const uint32_t *__restrict__ ent, const uint32_t *__restrict__ ebkt,
-             const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__restrict__ buckets,
+             const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *__restrict__ buckets,
              XYZZ<F> *__restrict__ parts)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t E = start[B];
+    const uint32_t S = msm_run_length(E, rmax);
     const uint64_t lo64 = (uint64_t)t * S;
     if (lo64 >= E) return;
     const uint32_t lo = (uint32_t)lo64;
@@ -52,9 +53,9 @@ k_accumulate(const Affine<F> *__restrict__ pts, const uint32_t *__restrict__ ent
 
 template <class F>
 int launch_accumulate(zkb_ctx *ctx, const Affine<F> *pts, const uint32_t *ent, const uint32_t *ebkt,
-                      const uint32_t *start, uint32_t B, uint32_t S, XYZZ<F> *buckets, XYZZ<F> *parts, size_t runs)
+                      const uint32_t *start, uint32_t B, uint32_t rmax, XYZZ<F> *buckets, XYZZ<F> *parts)
 {
-    k_accumulate<F><<<ceil_div(runs, 128), 128, 0, ctx->stream>>>(pts, ent, ebkt, start, B, S, buckets, parts);
+    k_accumulate<F><<<ceil_div(rmax, 128), 128, 0, ctx->stream>>>(pts, ent, ebkt, start, B, rmax, buckets, parts);
     ZKB_LAUNCH_CHECK(ctx);
     return ZKB_OK;
 }

@@ -24,13 +24,14 @@ template <class PT> __device__ __forceinline__ PT sm_get(const uint32_t *sm, int
 // One lane per bucket for short spans, the whole warp for medium spans; a bucket that spans very many runs
 // (the "scalar == 1" bucket of a Groth16 witness holds thousands of pairs) is queued for k_fixup_wide, where a
 // whole thread block reduces it.
-constexpr int FIXUP_T = 128, FIXUP_WARP = 8, FIXUP_BLOCK = 256;
+constexpr int FIXUP_T = 128, FIXUP_WARP = 8, FIXUP_WARP_ALWAYS = 64, FIXUP_BLOCK = 256;
 template <class F>
 __global__ void __launch_bounds__(FIXUP_T)
-k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__restrict__ buckets,
+k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *__restrict__ buckets,
         const XYZZ<F> *__restrict__ parts, uint32_t *__restrict__ wide_list)
 {
     extern __shared__ uint32_t sm[];
+    const uint32_t S = msm_run_length(start[B], rmax);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t *wsm = sm + (size_t)wid * 32 * (sizeof(XYZZ<F>) / 4);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -50,8 +51,12 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__r
             multi = t1 > t0;
         }
     }
+    // medium spans: the warp takes them one after another when only a few of its lanes have one (isolated heavy
+    // buckets), each lane keeps its own when most lanes do (uniformly filled windows)
     const bool block_wide = multi && (t1 - t0) >= FIXUP_BLOCK;
-    const bool wide = multi && !block_wide && (t1 - t0) >= FIXUP_WARP;
+    const bool medium = multi && !block_wide && (t1 - t0) >= FIXUP_WARP;
+    const int n_medium = __popc(__ballot_sync(0xffffffffu, medium));
+    const bool wide = medium && ((t1 - t0) >= FIXUP_WARP_ALWAYS || n_medium <= 4);
     if (block_wide) wide_list[1 + atomicAdd(wide_list, 1u)] = b;
     if (multi && !wide && !block_wide) {
         XYZZ<F> acc = ld_vec(parts + 2 * (size_t)t0 + ((s == t0 * S) ? 0 : 1));
@@ -88,10 +93,11 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t S, XYZZ<F> *__r
 // the queued buckets, one thread block each (grid-stride over the queue)
 template <class F>
 __global__ void __launch_bounds__(FIXUP_T)
-k_fixup_wide(const uint32_t *__restrict__ start, uint32_t S, XYZZ<F> *__restrict__ buckets,
+k_fixup_wide(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *__restrict__ buckets,
              const XYZZ<F> *__restrict__ parts, const uint32_t *__restrict__ wide_list)
 {
     extern __shared__ uint32_t sm[];
+    const uint32_t S = msm_run_length(start[B], rmax);
     const int T = blockDim.x, t = threadIdx.x;
     const uint32_t count = wide_list[0];
     for (uint32_t i = blockIdx.x; i < count; i += gridDim.x) {
@@ -259,7 +265,7 @@ k_next_copy(const Affine<F> *__restrict__ prev, Affine<F> *__restrict__ next, si
 }
 
 template <class F>
-int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t S, size_t ctx_runs_hint, XYZZ<F> *d_res)
+int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t rmax, XYZZ<F> *d_res)
 {
     typedef XYZZ<F> PT;
     cudaStream_t st = ctx->stream;
@@ -269,15 +275,15 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
     PT *parts = ctx->scratch[gs + SB_PARTS].as<PT>();
     PT *buckets = ctx->scratch[gs + SB_BUCKETS].as<PT>();
     // queue of buckets for the block-wide fix-up: a bucket enters it when it spans >= FIXUP_BLOCK runs
-    const size_t max_wide = (size_t)((uint64_t)ctx_runs_hint / FIXUP_BLOCK) + 1;
+    const size_t max_wide = (size_t)rmax / FIXUP_BLOCK + 1;
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_WIDE].ensure((max_wide + 1) * 4));
     uint32_t *wide = ctx->scratch[gs + SB_WIDE].as<uint32_t>();
     ZKB_CUDA(ctx, cudaMemsetAsync(wide, 0, 4, st));
-    k_fixup<F><<<ceil_div(B, FIXUP_T), FIXUP_T, (FIXUP_T / 32) * 32 * sizeof(PT), st>>>(start, (uint32_t)B, S, buckets, parts, wide);
+    k_fixup<F><<<ceil_div(B, FIXUP_T), FIXUP_T, (FIXUP_T / 32) * 32 * sizeof(PT), st>>>(start, (uint32_t)B, rmax, buckets, parts, wide);
     ZKB_LAUNCH_CHECK(ctx);
     {
         size_t wblocks = max_wide < (size_t)ctx->sm_count * 2 ? max_wide : (size_t)ctx->sm_count * 2;
-        k_fixup_wide<F><<<(unsigned)wblocks, FIXUP_T, FIXUP_T * sizeof(PT), st>>>(start, S, buckets, parts, wide);
+        k_fixup_wide<F><<<(unsigned)wblocks, FIXUP_T, FIXUP_T * sizeof(PT), st>>>(start, (uint32_t)B, rmax, buckets, parts, wide);
         ZKB_LAUNCH_CHECK(ctx);
     }
     for (uint32_t q = 0; q < tab.njobs; q++) {
@@ -289,7 +295,7 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
         const int T = (int)(nb < 128 ? nb : 128);
         const size_t all_buckets = (size_t)nb * J.G * batch;
         int L = 1;
-        while (L < 8 && L < (int)(nb / T) && all_buckets / (2 * L) >= (size_t)ctx->sm_count * 1024) L <<= 1;
+        while (L < 8 && L < (int)(nb / T) && all_buckets / (2 * L) >= (size_t)ctx->sm_count * 512) L <<= 1;
         while (nb / ((uint32_t)T * L) > 128) L <<= 1; // level 2 handles at most 128 level-1 blocks per set
         const int NB = (int)(nb / ((uint32_t)T * L));
         if (NB > 128) return fail(ctx, ZKB_ERR_ARG, "msm: window too wide for the bucket reduction");

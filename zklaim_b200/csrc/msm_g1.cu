@@ -2,7 +2,7 @@
 #define ZKB_NOINLINE_MUL 1
 #include "msm_finish_impl.cuh"
 namespace zkb {
-template int msm_finish<Fq>(zkb_ctx *, const MsmPlan *, const JobTab &, int, uint32_t, size_t, XYZZ<Fq> *);
+template int msm_finish<Fq>(zkb_ctx *, const MsmPlan *, const JobTab &, int, uint32_t, XYZZ<Fq> *);
 template int plan_upload_job<Fq>(zkb_ctx *, MsmPlan *, int, const uint64_t *, bool);
 template int results_to_host<Fq>(zkb_ctx *, const XYZZ<Fq> *, size_t, uint64_t *);
 }

@@ -53,11 +53,11 @@ int msm_sort_pairs(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const u
 // msm_acc_g1.cu / msm_g2.cu: bucket accumulation over fixed-length runs of the sorted pair list
 template <class F>
 int launch_accumulate(zkb_ctx *ctx, const Affine<F> *pts, const uint32_t *ent, const uint32_t *ebkt,
-                      const uint32_t *start, uint32_t B, uint32_t S, XYZZ<F> *buckets, XYZZ<F> *parts, size_t runs);
+                      const uint32_t *start, uint32_t B, uint32_t rmax, XYZZ<F> *buckets, XYZZ<F> *parts);
 
 // msm_g1.cu / msm_g2.cu: fix-up, bucket reduction, per-job result (XYZZ, device, [batch][njobs]); base precomputation
 template <class F>
-int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t S, size_t runs, XYZZ<F> *d_res);
+int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t rmax, XYZZ<F> *d_res);
 template <class F> int plan_upload_job(zkb_ctx *ctx, MsmPlan *plan, int job, const uint64_t *affine, bool from_device = false);
 template <class F> int results_to_host(zkb_ctx *ctx, const XYZZ<F> *d_res, size_t count, uint64_t *out_jacobian);
 
@@ -66,13 +66,16 @@ template <class F>
 int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t *d_plain, size_t zstride, int batch,
             XYZZ<F> *d_res);
 
-inline uint32_t msm_run_length(const zkb_ctx *ctx, size_t Emax)
+// Run length of the bucket accumulation: the sorted pair list (E pairs, known on the device only) is cut into at
+// most `rmax` runs of S = 4, 8, 16, ... pairs; every kernel derives S from E the same way.
+__host__ __device__ inline uint32_t msm_run_length(uint32_t E, uint32_t rmax)
 {
-    // longest run (fewest boundary partials for the fix-up pass) that still leaves two waves of threads
-    uint32_t S = 256;
-    while (S > 4 && Emax / S < (size_t)ctx->sm_count * 2048) S >>= 1;
+    uint32_t S = 4;
+    while ((uint64_t)S * rmax < E) S <<= 1;
     return S;
 }
+// runs per MSM launch: four waves of accumulation threads
+inline uint32_t msm_max_runs(const zkb_ctx *ctx) { return (uint32_t)ctx->sm_count * 2048u; }
 
 } // namespace zkb
 

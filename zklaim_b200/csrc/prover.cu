@@ -29,6 +29,7 @@
 #include "msm_impl.cuh"
 #include "ntt.cuh"
 #include <string.h>
+#include <algorithm>
 
 using namespace zkb;
 
@@ -38,6 +39,8 @@ struct zkb_key {
     int kind = 0;
     Domain dom;
     uint32_t *rowptr[3] = {nullptr, nullptr, nullptr};
+    uint32_t *rowperm[3] = {nullptr, nullptr, nullptr};
+    uint32_t nlong[3] = {0, 0, 0};
     uint32_t *col[3] = {nullptr, nullptr, nullptr};
     Fr *coeff[3] = {nullptr, nullptr, nullptr};
     size_t nnz[3] = {0, 0, 0};
@@ -62,6 +65,8 @@ struct CsrDev {
     const uint32_t *rowptr[3];
     const uint32_t *col[3];
     const Fr *coeff[3];
+    const uint32_t *perm[3]; // rows by decreasing length
+    uint32_t nlong[3];       // how many of them have >= SPMV_LONG terms
 };
 
 __device__ __forceinline__ bool is_mont_one(const Fr &a)
@@ -74,25 +79,54 @@ __device__ __forceinline__ bool is_mont_one(const Fr &a)
 
 // abc[(mat * batch + p) * m + row] = <row of matrix mat, z_p>; rows >= nc: the input-consistency
 // constraints of r1cs_to_qap.tcc:228-231 for A, zero for B and C.
-__global__ void __launch_bounds__(128)
-k_spmv(CsrDev csr, const Fr *__restrict__ Z, size_t zlen, size_t nc, size_t ni, size_t m, int batch, Fr *__restrict__ abc)
+// Rows are visited in order of decreasing length (csr.perm, built at key upload) so that the threads of a
+// warp see rows of equal length; the csr.nlong[mat] longest rows (>= SPMV_LONG terms: the packing
+// constraints of the SHA-256 / comparison gadgets) get a whole warp each.
+constexpr int SPMV_LONG = 48;
+__device__ __forceinline__ Fr spmv_term(const CsrDev &csr, int mat, const Fr *__restrict__ z, uint32_t e)
 {
-    const size_t row = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (row >= m) return;
+    const Fr c = ld_vec_ro(csr.coeff[mat] + e);
+    const Fr x = ld_vec(z + csr.col[mat][e]);
+    return is_mont_one(c) ? x : c * x;
+}
+__global__ void __launch_bounds__(128)
+k_spmv(CsrDev csr, uint32_t long_blocks, const Fr *__restrict__ Z, size_t zlen, size_t nc, size_t ni, size_t m, int batch,
+       Fr *__restrict__ abc)
+{
     const int mat = blockIdx.y, p = blockIdx.z;
     const Fr *z = Z + (size_t)p * zlen;
-    Fr acc = Fr::zero();
-    if (row < nc) {
+    Fr *out = abc + ((size_t)mat * batch + p) * m;
+    const uint32_t nlong = csr.nlong[mat];
+    if (blockIdx.x < long_blocks) {
+        const uint32_t w = blockIdx.x * 4 + (threadIdx.x >> 5);
+        const int lane = threadIdx.x & 31;
+        if (w >= nlong) return;
+        const uint32_t row = csr.perm[mat][w];
         const uint32_t lo = csr.rowptr[mat][row], hi = csr.rowptr[mat][row + 1];
-        for (uint32_t e = lo; e < hi; e++) {
-            const Fr c = ld_vec_ro(csr.coeff[mat] + e);
-            const Fr x = ld_vec(z + csr.col[mat][e]);
-            acc = acc + (is_mont_one(c) ? x : c * x);
+        Fr acc = Fr::zero();
+        for (uint32_t e = lo + lane; e < hi; e += 32) acc = acc + spmv_term(csr, mat, z, e);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            Fr o;
+#pragma unroll
+            for (int i = 0; i < 8; i++) o.v[i] = __shfl_down_sync(0xffffffffu, acc.v[i], d);
+            acc = acc + o;
         }
-    } else if (mat == 0 && row - nc <= ni) {
-        acc = ld_vec(z + (row - nc));
+        if (lane == 0) st_vec(out + row, acc);
+        return;
     }
-    st_vec(abc + ((size_t)mat * batch + p) * m + row, acc);
+    const size_t s = (size_t)(blockIdx.x - long_blocks) * blockDim.x + threadIdx.x + nlong;
+    if (s >= m) return;
+    Fr acc = Fr::zero();
+    size_t row = s;
+    if (s < nc) {
+        row = csr.perm[mat][s];
+        const uint32_t lo = csr.rowptr[mat][row], hi = csr.rowptr[mat][row + 1];
+        for (uint32_t e = lo; e < hi; e++) acc = acc + spmv_term(csr, mat, z, e);
+    } else if (mat == 0 && s - nc <= ni) {
+        acc = ld_vec(z + (s - nc));
+    }
+    st_vec(out + row, acc);
 }
 
 // r1cs_constraint_system::is_satisfied (r1cs.tcc): <a,z> * <b,z> == <c,z> for every constraint
@@ -212,6 +246,23 @@ int upload_csr(zkb_ctx *ctx, zkb_key *key, int mat, const zkb_csr &h)
     ZKB_CUDA(ctx, cudaMalloc(&key->coeff[mat], (nnz + 1) * sizeof(Fr)));
     key->bytes += (nc + 1) * 4 + (nnz + 1) * 36;
     ZKB_CUDA(ctx, cudaMemcpy(key->rowptr[mat], rp.data(), (nc + 1) * 4, cudaMemcpyHostToDevice));
+    // rows by decreasing length (counting sort on the length, stable)
+    {
+        uint32_t maxlen = 0;
+        for (size_t i = 0; i < nc; i++) maxlen = std::max(maxlen, rp[i + 1] - rp[i]);
+        std::vector<uint32_t> cnt((size_t)maxlen + 2, 0), perm(nc + 1);
+        for (size_t i = 0; i < nc; i++) cnt[maxlen - (rp[i + 1] - rp[i]) + 1]++;
+        for (size_t l = 1; l < cnt.size(); l++) cnt[l] += cnt[l - 1];
+        key->nlong[mat] = 0;
+        for (size_t i = 0; i < nc; i++) {
+            const uint32_t len = rp[i + 1] - rp[i];
+            perm[cnt[maxlen - len]++] = (uint32_t)i;
+            if (len >= (uint32_t)SPMV_LONG) key->nlong[mat]++;
+        }
+        ZKB_CUDA(ctx, cudaMalloc(&key->rowperm[mat], (nc + 1) * 4));
+        ZKB_CUDA(ctx, cudaMemcpy(key->rowperm[mat], perm.data(), nc * 4, cudaMemcpyHostToDevice));
+        key->bytes += (nc + 1) * 4;
+    }
     if (nnz) {
         ZKB_CUDA(ctx, cudaMemcpy(key->col[mat], h.col, nnz * 4, cudaMemcpyHostToDevice));
         ZKB_CUDA(ctx, cudaMemcpy(key->coeff[mat], h.coeff, nnz * sizeof(Fr), cudaMemcpyHostToDevice));
@@ -228,6 +279,7 @@ void key_release(zkb_key *key)
     cudaSetDevice(key->dev);
     for (int k = 0; k < 3; k++) {
         if (key->rowptr[k]) cudaFree(key->rowptr[k]);
+        if (key->rowperm[k]) cudaFree(key->rowperm[k]);
         if (key->col[k]) cudaFree(key->col[k]);
         if (key->coeff[k]) cudaFree(key->coeff[k]);
     }
@@ -398,8 +450,11 @@ int witness_map_chunk(zkb_ctx *ctx, const zkb_key *key, int batch, uint32_t *d_f
         csr.rowptr[k] = key->rowptr[k];
         csr.col[k] = key->col[k];
         csr.coeff[k] = key->coeff[k];
+        csr.perm[k] = key->rowperm[k];
+        csr.nlong[k] = key->nlong[k];
     }
-    k_spmv<<<dim3(ceil_div(m, 128), 3, batch), 128, 0, st>>>(csr, Z, key->zlen, key->nc, key->ni, m, batch, abc);
+    const uint32_t long_blocks = (std::max(key->nlong[0], std::max(key->nlong[1], key->nlong[2])) + 3) / 4;
+    k_spmv<<<dim3(long_blocks + ceil_div(m, 128), 3, batch), 128, 0, st>>>(csr, long_blocks, Z, key->zlen, key->nc, key->ni, m, batch, abc);
     ZKB_LAUNCH_CHECK(ctx);
     if (key->nc) {
         k_sat_check<<<dim3(ceil_div(key->nc, 128), batch), 128, 0, st>>>(abc, key->nc, m, batch, d_flags);
