@@ -7,9 +7,9 @@ one proving key, one proof stream per GPU.  A step = one batch of 64 proofs on e
 
   value : proofs/s, witnesses already resident in HBM (zkb_prove_batch_device), whole job
   e2e   : proofs/s through the C ABI with HOST buffers (zkb_prove_batch: pinned witnesses in, proofs out)
-  roofline     : the dominant kernel (G1 bucket accumulation, k_accumulate<Fq>) against the measured integer
-                 multiply-add (IMAD) rate of the device -- this path is integer work, neither HBM- nor
-                 tensor-bound; its HBM fraction is reported beside it
+  roofline     : the dominant kernel (G1 bucket accumulation of the H + L query, k_accumulate<Fq>) against the
+                 measured integer multiply-add (IMAD.WIDE) rate of the device -- this path is integer work, neither
+                 HBM- nor tensor-bound; its HBM fraction is reported beside it
   cpu_baseline : the reference's own libsnark prover (oracle/_ref, -DMULTICORE -DUSE_ASM) on the host cores
 
 `--impl reference` times the reference CPU prover instead (same workload, bounded sample per step).
@@ -254,6 +254,11 @@ def run_ours(args):
         return
     peaks, peak_kind = measured_peaks()
     imad_peak = ctx.imad_peak(1024)
+    try:  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (profiles/)
+        with open(os.path.join(ROOT, "profiles", "k_accumulate_traffic.json")) as f:
+            traffic = json.load(f)["traffic_bytes_per_launch"]
+    except Exception:
+        traffic = None
     acc_s = prof["g1_ms"] * 1e-3 / max(prof["g1_launches"], 1)
     pairs = prof["g1_pairs"] / max(prof["g1_launches"], 1)
     achieved = pairs * MUL_PER_MADD_REF * IMAD_PER_MUL / acc_s
@@ -262,7 +267,9 @@ def run_ours(args):
         "achieved": achieved / 1e9, "peak": imad_peak / 1e9, "unit": "GIMAD/s", "frac": achieved / imad_peak,
         "peak_source": "chains of dependent Montgomery products (136 wide multiply-adds each) on all SMs, measured live (zkb_measure_imad_peak); nominal 148 SM x 32 IMAD.WIDE/clk x 1.965 GHz = 9310 GIMAD/s",
         "achieved_executed": pairs * MUL_PER_MADD_XYZZ * IMAD_PER_MUL / acc_s / 1e9,
-        "units_per_launch": pairs, "ms_per_launch": acc_s * 1e3, "traffic": None,
+        "frac_executed": pairs * MUL_PER_MADD_XYZZ * IMAD_PER_MUL / acc_s / imad_peak,
+        "units_per_launch": pairs, "ms_per_launch": acc_s * 1e3, "traffic": traffic,
+        "algorithmic": "one mixed addition per (point, window) pair = 11 Fq products (reference formulas) x 136 multiply-adds; executed: 10 (XYZZ)",
         "hbm": {"achieved": pairs * BYTES_PER_PAIR / acc_s / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": pairs * BYTES_PER_PAIR / acc_s / 1e9 / peaks["hbm_gbs"], "peak_source": peak_kind},
         "step_share": prof["g1_ms"] / max(prof["g1_launches"], 1) / (dev_ms / args.steps),

@@ -88,6 +88,11 @@ int zkb_group_op(zkb_ctx *ctx, int group, int op, const uint64_t *a, const uint6
 int zkb_group_scalar_mul(zkb_ctx *ctx, int group, const uint64_t *scalars, const uint64_t *points, uint64_t *out,
                          size_t n);
 
+/* Sum of n Jacobian points -- the final loop of libff::multi_exp over its per-chunk partial results
+ * (multiexp.tcc:433-438).  This is the combine step of an MSM whose point range is sharded over several GPUs:
+ * every rank computes zkb_msm on its range, the 96- / 192-byte partials are gathered, one rank sums them. */
+int zkb_group_sum(zkb_ctx *ctx, int group, const uint64_t *points, size_t n, uint64_t *out);
+
 /* ---- K4/K5: multi-scalar multiplication ------------------------------------------- */
 /* Uploads n affine bases and (precompute_factor > 1) their 2^(j*G*c) multiples so that up
  * to `precompute_factor` windows share one bucket set (HBM for doublings; B200 has 180 GB).

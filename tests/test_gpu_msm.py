@@ -93,3 +93,25 @@ def test_msm_linearity_at_scale(zctx, ref):
     s = ref.group_op(zk.G1, 0, ra[None], rb[None])[0]
     _check(ref, zk.G1, s, rab)
     B.free()
+
+
+@pytest.mark.parametrize("group,n", [(zk.G1, 5003), (zk.G2, 700)])
+def test_range_sharded_msm_equals_whole(zctx, ref, group, n):
+    """contiguous ranges (libff's chunking, multiexp.tcc:417-431) evaluated separately, partials
+    summed with zkb_group_sum (multiexp.tcc:433-438) == the whole MSM == the reference.  One GPU plays every rank."""
+    from zklaim_b200 import sharding
+    bases = ref.bases(group, 1 << 40, n)
+    s = ref.sha512_rng(5 << 32, n)
+    exp, _ = ref.msm(group, bases, s)
+    for world in (1, 2, 3, 8):
+        parts = []
+        for rank in range(world):
+            lo, hi = sharding.shard_range(n, rank, world)
+            B = zctx.upload_bases(group, bases[lo:hi])
+            parts.append(sharding.sharded_msm(zctx, group, B, s[lo:hi]))  # no process group: world of one per call
+            B.free()
+        _check(ref, group, zctx.group_sum(group, np.stack(parts)), exp)
+    w = 12 if group == zk.G1 else 24
+    zero = zctx.group_sum(group, np.zeros((0, w), dtype=np.uint64))
+    _check(ref, group, zero, ref.group_op(group, 0, zero[None], zero[None])[0])  # 0 + 0 == 0: it is the identity
+    _check(ref, group, zctx.group_sum(group, np.stack([exp, zero])), exp)

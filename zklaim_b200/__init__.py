@@ -43,6 +43,7 @@ SYMBOLS = {
     "zkb_field_op": (_i, [_vp, _i, _i, _u64p, _u64p, _u64p, _sz]),
     "zkb_group_op": (_i, [_vp, _i, _i, _u64p, _u64p, _u64p, _sz]),
     "zkb_group_scalar_mul": (_i, [_vp, _i, _u64p, _u64p, _u64p, _sz]),
+    "zkb_group_sum": (_i, [_vp, _i, _u64p, _sz, _u64p]),
     "zkb_bases_upload": (_i, [_vp, _i, _u64p, _sz, _i, _i, C.POINTER(_vp)]),
     "zkb_bases_free": (None, [_vp]),
     "zkb_bases_device_bytes": (_sz, [_vp]),
@@ -199,6 +200,14 @@ class Context:
         return out
 
     # ---- MSM --------------------------------------------------------------------------
+    def group_sum(self, group: int, points) -> np.ndarray:
+        """sum of Jacobian points (multiexp.tcc:433-438): the combine step of a range-sharded MSM"""
+        w = 12 if group == G1 else 24
+        p = _arr(points, w)
+        out = np.zeros(w, dtype=np.uint64)
+        self._chk(self.lib.zkb_group_sum(self.h, group, p.ctypes.data, p.size // w, out.ctypes.data))
+        return out
+
     def upload_bases(self, group: int, affine, window_bits: int = 0, precompute_factor: int = 0) -> "Bases":
         w = 8 if group == G1 else 16
         a = _arr(affine, w)

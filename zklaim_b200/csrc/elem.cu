@@ -71,6 +71,25 @@ template <class F> __global__ void k_group_op(int op, const Jacobian<F> *a, cons
     st_vec(o + i, x.to_jacobian());
 }
 
+// o[0] = sum of n Jacobian points (one block; the partial sums of a range-sharded MSM, multiexp.tcc:433-438)
+template <class F> __global__ void __launch_bounds__(32) k_group_sum(const Jacobian<F> *a, Jacobian<F> *o, size_t n)
+{
+    __shared__ XYZZ<F> sh[32];
+    const int t = threadIdx.x;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (size_t i = t; i < n; i += 32) acc.add(XYZZ<F>::from_jacobian(ld_vec(a + i)));
+    sh[t] = acc;
+    __syncwarp();
+    for (int d = 16; d > 0; d >>= 1) {
+        if (t < d) {
+            acc.add(sh[t + d]);
+            sh[t] = acc;
+        }
+        __syncwarp();
+    }
+    if (t == 0) st_vec(o, acc.to_jacobian());
+}
+
 template <class F> __global__ void k_scalar_mul(const Fr *s, const Jacobian<F> *p, Jacobian<F> *o, size_t n)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -143,6 +162,27 @@ int zkb_group_op(zkb_ctx *ctx, int group, int op, const uint64_t *a, const uint6
         k_group_op<Fq2><<<g, 64, 0, ctx->stream>>>(op, (const G2J *)da, (const G2J *)db, (G2J *)d_o, n);
     ZKB_LAUNCH_CHECK(ctx);
     ZKB_CUDA(ctx, cudaMemcpyAsync(out, d_o, n * es, cudaMemcpyDeviceToHost, ctx->stream));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ZKB_OK;
+}
+
+int zkb_group_sum(zkb_ctx *ctx, int group, const uint64_t *points, size_t n, uint64_t *out)
+{
+    if (!ctx || !out || (!points && n) || (group != ZKB_G1 && group != ZKB_G2))
+        return fail(ctx, ZKB_ERR_ARG, "zkb_group_sum: bad argument");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    const size_t es = group == ZKB_G1 ? 96 : 192;
+    void *da = nullptr;
+    int rc;
+    if (n && (rc = stage(ctx, SB_A, points, n * es, &da))) return rc;
+    ZKB_CUDA(ctx, ctx->scratch[SB_O].ensure(es));
+    void *d_o = ctx->scratch[SB_O].p;
+    if (group == ZKB_G1)
+        k_group_sum<Fq><<<1, 32, 0, ctx->stream>>>((const G1J *)da, (G1J *)d_o, n);
+    else
+        k_group_sum<Fq2><<<1, 32, 0, ctx->stream>>>((const G2J *)da, (G2J *)d_o, n);
+    ZKB_LAUNCH_CHECK(ctx);
+    ZKB_CUDA(ctx, cudaMemcpyAsync(out, d_o, es, cudaMemcpyDeviceToHost, ctx->stream));
     ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return ZKB_OK;
 }

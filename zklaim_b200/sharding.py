@@ -1,0 +1,67 @@
+"""Range sharding of a multi-scalar multiplication over the GPUs of one node.
+
+libff::multi_exp already has this shape on the CPU (multiexp.tcc:402-441): the point / scalar vectors are cut into
+`chunks` contiguous ranges of `total / chunks` items (the last one takes the remainder), every range is evaluated
+independently (`#pragma omp parallel for`), and the per-range results are added up (:433-438).  Here a range is
+a GPU: one process per GPU (torch.distributed), every rank uploads the bases of ITS range only and evaluates it
+with libzkb.so; the only exchange is an all_gather of one Jacobian point per rank (96 bytes in G1, 192 in G2),
+after which every rank holds all partials and the sum is n - 1 point additions (zkb_group_sum).  NCCL's reduce
+operators do not apply -- the group law is not a limb-wise sum -- so the collective is a gather, and the data
+path itself needs none: this is the "tiny reduction of partial sums" of the north star.
+
+No arithmetic lives in this file; without libzkb.so / a GPU the combine step raises like everything else.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Tuple
+
+import numpy as np
+
+from . import G1, G2
+
+
+def shard_range(total: int, rank: int, world: int) -> Tuple[int, int]:
+    """[lo, hi) of rank `rank`: libff's chunking (multiexp.tcc:417-431) -- `total // world` items each, the last
+    rank also takes the remainder; with fewer items than ranks rank 0 takes everything (:411-416)."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("bad rank / world size")
+    if total < world or world == 1:
+        return (0, total) if rank == 0 else (0, 0)
+    one = total // world
+    lo = rank * one
+    hi = total if rank == world - 1 else lo + one
+    return lo, hi
+
+
+def gather_partials(partial: np.ndarray, group=None, device: Optional[str] = None) -> np.ndarray:
+    """all_gather of one Jacobian point per rank -> (world, 12 | 24) uint64, identical on every rank.
+    `group` is a torch.distributed process group (None = the default one; no process group = world of one).
+    With the nccl backend the 96 / 192 bytes travel through a device tensor on `device`."""
+    import torch
+    import torch.distributed as dist
+
+    p = np.ascontiguousarray(partial, dtype=np.uint64)
+    if not (dist.is_available() and dist.is_initialized()):
+        return p[None].copy()
+    world = dist.get_world_size(group)
+    backend = dist.get_backend(group)
+    dev = torch.device(device if device is not None else ("cuda" if backend == "nccl" else "cpu"))
+    mine = torch.from_numpy(p.view(np.int64).copy()).to(dev)
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine, group=group)
+    return np.stack([t.cpu().numpy().view(np.uint64) for t in out])
+
+
+def sharded_msm(ctx, group_id: int, bases_local, scalars_local: np.ndarray, group=None, device: Optional[str] = None,
+                combine: Optional[Callable[[int, np.ndarray], np.ndarray]] = None) -> np.ndarray:
+    """sum_i s_i P_i over ALL ranks' ranges.  `bases_local` = this rank's zkb Bases (uploaded from its
+    shard_range), `scalars_local` the matching scalars.  Returns the Jacobian limbs of the total on every rank.
+    `combine(group_id, partials)` defaults to the GPU (ctx.group_sum)."""
+    if group_id not in (G1, G2):
+        raise ValueError("group_id must be G1 or G2")
+    if len(scalars_local):
+        part = ctx.msm(bases_local, scalars_local)
+    else:  # an empty range contributes the zero of the group, (0, 1, 0) in Montgomery form (alt_bn128_init.cpp:145-147)
+        part = ctx.group_sum(group_id, np.zeros((0, 12 if group_id == G1 else 24), dtype=np.uint64))
+    parts = gather_partials(part, group, device)
+    return (combine or ctx.group_sum)(group_id, parts)
