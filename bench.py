@@ -250,7 +250,11 @@ def run_ours(args):
     prof = ctx.profile_read()
     ctx.profile(False)
 
+    if world > 1:
+        dist.barrier()
     if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
         return
     peaks, peak_kind = measured_peaks()
     imad_peak = ctx.imad_peak(1024)
@@ -303,6 +307,8 @@ def run_ours(args):
         "key_device_mb": key.device_bytes() / 1e6,
     }
     print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def main():

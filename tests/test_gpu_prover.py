@@ -109,6 +109,57 @@ def test_key_tune_dense_witness(zctx, ref):
     circ.free()
 
 
+def test_blinding_edge_values(zctx, ref):
+    """(r, s) = (0, 1), (1, 0), (r - 1, 2), (17, 16): the windowed scalar multiplications s * g1_A and r * g1_B
+    (r1cs_gg_ppzksnark.tcc:495) with empty / single / all-ones / colliding 4-bit windows."""
+    circ = ref.Circuit.example(253, 5, seed=3)
+    circ.setup()
+    key = zctx.upload_key(circ.export_key())
+    w = circ.witness()
+    zero = np.zeros(4, dtype=np.uint64)
+    one = ref.field_const(zk.FR, 1)
+    small = lambda v: ref.from_plain(zk.FR, np.array([[v, 0, 0, 0]], dtype=np.uint64))[0]
+    minus1 = ref.field_op(zk.FR, 1, zero[None], one[None])[0]
+    for r, s in ((zero, one), (one, zero), (minus1, small(2)), (small(17), small(16)), (zero, zero)):
+        exp = circ.prove(w, r, s, want_H=False)
+        got = zctx.prove(key, w, r, s)
+        assert ref.proof_bytes(got) == ref.proof_bytes(exp["proof"])
+    key.free()
+    circ.free()
+
+
+def test_batch_larger_than_one_chunk(zctx, ref):
+    """zkb_prove_batch cuts a batch into chunks of at most 64 proofs: 70 proofs of a small circuit with distinct
+    (r, s); proofs 0, 63, 64 and 69 (both sides of the chunk boundary) against the reference."""
+    circ = ref.Circuit.example(253, 5, seed=3)
+    circ.setup()
+    key = zctx.upload_key(circ.export_key())
+    w = circ.witness()
+    n = 70
+    ws = np.stack([w] * n)
+    r = ref.sha512_rng(7000, n)
+    s = ref.sha512_rng(8000, n)
+    got = zctx.prove_batch(key, ws, r, s)
+    for i in (0, 63, 64, 69):
+        exp = circ.prove(w, r[i], s[i], want_H=False)
+        assert ref.proof_bytes(got[i]) == ref.proof_bytes(exp["proof"]), i
+    key.free()
+    circ.free()
+
+
+def test_sha_chain_circuit(zctx, ref):
+    """BASELINE configs[4] in miniature: two chained sha256_two_to_one_hash_gadget blocks (54 560 constraints, 256 public
+    inputs, domain 2^16), key tuned; the full-size run (153 blocks, 2^22) is scripts/s22_prove.py, profiles/r01_s22_full_prove.txt"""
+    circ = ref.Circuit.sha_chain(2, 11)
+    assert circ.is_satisfied()
+    circ.setup()
+    key = zctx.upload_key(circ.export_key())
+    key.tune(circ.witness())
+    _check_against_reference(zctx, ref, circ, key, circ.witness(), 515)
+    key.free()
+    circ.free()
+
+
 def test_unsatisfied_witness_is_reported(zctx, ref, zklaim1):
     circ, key = zklaim1
     w = circ.witness().copy()
@@ -119,7 +170,7 @@ def test_unsatisfied_witness_is_reported(zctx, ref, zklaim1):
     assert e.value.code == zk.ERR_UNSAT
 
 
-@pytest.mark.parametrize("nc,ni", [(20, 3), (1013, 10), (2048 - 11, 10), (2048 + 256 - 11, 10), (5000, 100)])
+@pytest.mark.parametrize("nc,ni", [(20, 3), (1013, 10), (2048 - 11, 10), (2048 + 256 - 11, 10), (5000, 100), (20000, 10)])
 def test_example_circuits_dense_witness(zctx, ref, nc, ni):
     circ = ref.Circuit.example(nc, ni, seed=nc)
     assert circ.is_satisfied()

@@ -45,6 +45,7 @@ struct zkb_ctx {
     cudaStream_t main_stream = nullptr;     // owns the timing events and every synchronisation with the host
     cudaStream_t side_stream[2] = {nullptr, nullptr}; // prover: witness-only MSMs overlap the witness map
     cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+    uint32_t func_attr_done = 0;            // cudaFuncSetAttribute calls already made on this device (bit per kernel)
     int lane_bias = 0;                      // scratch-slot offset of the active MSM lane
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;

@@ -24,7 +24,8 @@ template <class PT> __device__ __forceinline__ PT sm_get(const uint32_t *sm, int
 // One lane per bucket for short spans, the whole warp for medium spans; a bucket that spans very many runs
 // (the "scalar == 1" bucket of a Groth16 witness holds thousands of pairs) is queued for k_fixup_wide, where a
 // whole thread block reduces it.
-constexpr int FIXUP_T = 128, FIXUP_WARP = 8, FIXUP_WARP_ALWAYS = 64, FIXUP_BLOCK = 256;
+constexpr int FIXUP_WIDE_T = 256; // threads of a k_fixup_wide block
+constexpr int FIXUP_T = 128, FIXUP_WARP = 8, FIXUP_BLOCK = 64;
 template <class F>
 __global__ void __launch_bounds__(FIXUP_T)
 k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *__restrict__ buckets,
@@ -52,11 +53,12 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *
         }
     }
     // medium spans: the warp takes them one after another when only a few of its lanes have one (isolated heavy
-    // buckets), each lane keeps its own when most lanes do (uniformly filled windows)
+    // buckets), each lane keeps its own when most lanes do (uniformly filled windows); long spans go to the queue
+    // (neighbouring heavy buckets -- the small digits of window 0 -- would otherwise serialise inside one warp)
     const bool block_wide = multi && (t1 - t0) >= FIXUP_BLOCK;
     const bool medium = multi && !block_wide && (t1 - t0) >= FIXUP_WARP;
     const int n_medium = __popc(__ballot_sync(0xffffffffu, medium));
-    const bool wide = medium && ((t1 - t0) >= FIXUP_WARP_ALWAYS || n_medium <= 4);
+    const bool wide = medium && n_medium <= 4;
     if (block_wide) wide_list[1 + atomicAdd(wide_list, 1u)] = b;
     if (multi && !wide && !block_wide) {
         XYZZ<F> acc = ld_vec(parts + 2 * (size_t)t0 + ((s == t0 * S) ? 0 : 1));
@@ -92,7 +94,7 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *
 
 // the queued buckets, one thread block each (grid-stride over the queue)
 template <class F>
-__global__ void __launch_bounds__(FIXUP_T)
+__global__ void __launch_bounds__(FIXUP_WIDE_T)
 k_fixup_wide(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *__restrict__ buckets,
              const XYZZ<F> *__restrict__ parts, const uint32_t *__restrict__ wide_list)
 {
@@ -275,15 +277,20 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
     PT *parts = ctx->scratch[gs + SB_PARTS].as<PT>();
     PT *buckets = ctx->scratch[gs + SB_BUCKETS].as<PT>();
     // queue of buckets for the block-wide fix-up: a bucket enters it when it spans >= FIXUP_BLOCK runs
-    const size_t max_wide = (size_t)rmax / FIXUP_BLOCK + 1;
+    const size_t max_wide = (size_t)rmax / (FIXUP_BLOCK / 2) + 16; // a queued bucket owns >= FIXUP_BLOCK - 1 runs
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_WIDE].ensure((max_wide + 1) * 4));
     uint32_t *wide = ctx->scratch[gs + SB_WIDE].as<uint32_t>();
     ZKB_CUDA(ctx, cudaMemsetAsync(wide, 0, 4, st));
     k_fixup<F><<<ceil_div(B, FIXUP_T), FIXUP_T, (FIXUP_T / 32) * 32 * sizeof(PT), st>>>(start, (uint32_t)B, rmax, buckets, parts, wide);
     ZKB_LAUNCH_CHECK(ctx);
     {
+        const uint32_t attr_bit = plan->group == ZKB_G2 ? 4u : 2u; // function attributes are per device = per context
+        if (!(ctx->func_attr_done & attr_bit)) {
+            ZKB_CUDA(ctx, cudaFuncSetAttribute(k_fixup_wide<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FIXUP_WIDE_T * sizeof(PT))));
+            ctx->func_attr_done |= attr_bit;
+        }
         size_t wblocks = max_wide < (size_t)ctx->sm_count * 2 ? max_wide : (size_t)ctx->sm_count * 2;
-        k_fixup_wide<F><<<(unsigned)wblocks, FIXUP_T, FIXUP_T * sizeof(PT), st>>>(start, (uint32_t)B, rmax, buckets, parts, wide);
+        k_fixup_wide<F><<<(unsigned)wblocks, FIXUP_WIDE_T, FIXUP_WIDE_T * sizeof(PT), st>>>(start, (uint32_t)B, rmax, buckets, parts, wide);
         ZKB_LAUNCH_CHECK(ctx);
     }
     for (uint32_t q = 0; q < tab.njobs; q++) {

@@ -298,11 +298,10 @@ int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, si
 {
     const int L = T.logn;
     if (L == 0) return ZKB_OK;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaFuncSetAttribute(k_ntt_pass<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32);
-        cudaFuncSetAttribute(k_ntt_pass<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32);
-        attr_done = true;
+    if (!(ctx->func_attr_done & 1u)) { // per device = per context
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_pass<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_pass<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
+        ctx->func_attr_done |= 1u;
     }
     const int P = (L + NTT_KMAX - 1) / NTT_KMAX;
     int ks[8];

@@ -41,6 +41,11 @@ struct zkb_key {
     uint32_t *rowptr[3] = {nullptr, nullptr, nullptr};
     uint32_t *rowperm[3] = {nullptr, nullptr, nullptr};
     uint32_t nlong[3] = {0, 0, 0};
+    uint32_t ngiant[3] = {0, 0, 0};       // rows with >= SPMV_GIANT terms: cut into segments, one block each
+    uint32_t *giant_seg = nullptr;        // per segment: mat, row, e_lo, e_hi
+    uint32_t *giant_row = nullptr;        // per giant row: mat, row, first segment, segment count
+    uint32_t n_giant_seg = 0, n_giant_row = 0;
+    std::vector<uint32_t> h_giant_seg, h_giant_row; // staging while the three matrices are uploaded
     uint32_t *col[3] = {nullptr, nullptr, nullptr};
     Fr *coeff[3] = {nullptr, nullptr, nullptr};
     size_t nnz[3] = {0, 0, 0};
@@ -59,7 +64,7 @@ struct zkb_key {
 
 namespace {
 
-enum { SP_Z = SB_PROVER0, SP_P, SP_ABC, SP_TMP, SP_RS, SP_FLAGS, SP_PROOF, SP_W, SP_RES_AB, SP_RES_C, SP_RES2, SP_SMUL };
+enum { SP_Z = SB_PROVER0, SP_P, SP_ABC, SP_TMP, SP_RS, SP_FLAGS, SP_PROOF, SP_W, SP_RES_AB, SP_RES_C, SP_RES2, SP_SMUL, SP_GIANT };
 
 struct CsrDev {
     const uint32_t *rowptr[3];
@@ -67,6 +72,7 @@ struct CsrDev {
     const Fr *coeff[3];
     const uint32_t *perm[3]; // rows by decreasing length
     uint32_t nlong[3];       // how many of them have >= SPMV_LONG terms
+    uint32_t ngiant[3];      // the first ngiant of those are handled by k_spmv_giant
 };
 
 __device__ __forceinline__ bool is_mont_one(const Fr &a)
@@ -98,7 +104,7 @@ k_spmv(CsrDev csr, uint32_t long_blocks, const Fr *__restrict__ Z, size_t zlen, 
     Fr *out = abc + ((size_t)mat * batch + p) * m;
     const uint32_t nlong = csr.nlong[mat];
     if (blockIdx.x < long_blocks) {
-        const uint32_t w = blockIdx.x * 4 + (threadIdx.x >> 5);
+        const uint32_t w = blockIdx.x * 4 + (threadIdx.x >> 5) + csr.ngiant[mat];
         const int lane = threadIdx.x & 31;
         if (w >= nlong) return;
         const uint32_t row = csr.perm[mat][w];
@@ -127,6 +133,50 @@ k_spmv(CsrDev csr, uint32_t long_blocks, const Fr *__restrict__ Z, size_t zlen, 
         acc = ld_vec(z + (s - nc));
     }
     st_vec(out + row, acc);
+}
+
+// Rows with tens of thousands of terms (libsnark's example circuits end with one constraint over ALL variables;
+// r1cs_examples.tcc:70-90) are cut into segments of SPMV_GIANT_SEG terms: one block per (segment, proof) writes a
+// partial sum, k_spmv_giant_finish adds the partials of a row.
+constexpr int SPMV_GIANT = 8192, SPMV_GIANT_SEG = 4096;
+__global__ void __launch_bounds__(128)
+k_spmv_giant(CsrDev csr, const uint32_t *__restrict__ seg, const Fr *__restrict__ Z, size_t zlen, uint32_t nseg,
+             Fr *__restrict__ partial)
+{
+    __shared__ Fr sh[4];
+    const uint32_t g = blockIdx.x, p = blockIdx.y;
+    const int mat = (int)seg[4 * g], lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t lo = seg[4 * g + 2], hi = seg[4 * g + 3];
+    const Fr *z = Z + (size_t)p * zlen;
+    Fr acc = Fr::zero();
+    for (uint32_t e = lo + threadIdx.x; e < hi; e += blockDim.x) acc = acc + spmv_term(csr, mat, z, e);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        Fr o;
+#pragma unroll
+        for (int i = 0; i < 8; i++) o.v[i] = __shfl_down_sync(0xffffffffu, acc.v[i], d);
+        acc = acc + o;
+    }
+    if (lane == 0) sh[wid] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) st_vec(partial + (size_t)p * nseg + g, sh[0] + sh[1] + (sh[2] + sh[3]));
+}
+__global__ void __launch_bounds__(32)
+k_spmv_giant_finish(const uint32_t *__restrict__ rows, const Fr *__restrict__ partial, uint32_t nseg, size_t m, int batch,
+                    Fr *__restrict__ abc)
+{
+    const uint32_t g = blockIdx.x, p = blockIdx.y;
+    const uint32_t mat = rows[4 * g], row = rows[4 * g + 1], s0 = rows[4 * g + 2], cnt = rows[4 * g + 3];
+    Fr acc = Fr::zero();
+    for (uint32_t k = threadIdx.x; k < cnt; k += 32) acc = acc + ld_vec(partial + (size_t)p * nseg + s0 + k);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        Fr o;
+#pragma unroll
+        for (int i = 0; i < 8; i++) o.v[i] = __shfl_down_sync(0xffffffffu, acc.v[i], d);
+        acc = acc + o;
+    }
+    if (threadIdx.x == 0) st_vec(abc + ((size_t)mat * batch + p) * m + row, acc);
 }
 
 // r1cs_constraint_system::is_satisfied (r1cs.tcc): <a,z> * <b,z> == <c,z> for every constraint
@@ -178,34 +228,134 @@ __global__ void k_z_plain(const Fr *__restrict__ Z, Fr *__restrict__ P, size_t z
     st_vec(P + o, ld_vec(Z + o).from_mont());
 }
 
-// sm[2p] = s * g1_A, sm[2p + 1] = r * g1_B: the two variable-base scalar multiplications of
-// r1cs_gg_ppzksnark.tcc:495.  One warp each (a lone lane costs what a full warp costs; the chain of
-// doublings is serial): 4-bit fixed windows, the 15 multiples tabulated in shared memory.
-__global__ void __launch_bounds__(64)
-k_smul(const G1X *__restrict__ rab, const Fr *__restrict__ P, size_t zlen, size_t nv, G1X *__restrict__ sm)
+// ---- the two variable-base scalar multiplications of r1cs_gg_ppzksnark.tcc:495 ------------------------------
+// sm[2p] = s * g1_A, sm[2p + 1] = r * g1_B.  The chain of 252 doublings is serial and a warp instruction costs the
+// same for one active lane as for 32, so the parallelism available is INSIDE a point operation: the independent
+// field products of an XYZZ doubling (9 products, depth 3) and addition (14 products, depth 4) are spread over four
+// lanes that run one uniform instruction stream -- a tiny register machine whose registers live in shared memory.
+// An instruction = (op, dst, a, b) per lane and step; a step is either "every lane multiplies" or "every lane
+// adds / subtracts".  4-bit fixed windows; table entries are registers 32 + 4 d .. 32 + 4 d + 3.
+namespace vm {
+enum { MUL = 0, ADD = 1, SUB = 2, SUB2 = 3 /* a - b - b */, TRIPLE = 4 /* 3 a */, NOP = 5 };
+constexpr uint32_t ins(int op, int d, int a, int b) { return (uint32_t)op << 24 | (uint32_t)b << 16 | (uint32_t)a << 8 | (uint32_t)d; }
+constexpr int X = 0, Y = 1, ZZ = 2, ZZZ = 3, T0 = 4; // accumulator, temporaries T0 .. T0 + 11
+constexpr int Q = 0x40;                              // operand point: Q + 0 .. Q + 3 (resolved at run time)
+constexpr int DUMP = 28;                             // + lane: target of idle lanes
+constexpr uint32_t IDLE = ins(NOP, DUMP, X, X);
+// dbl-2008-s-1 (a = 0), see XYZZ::dbl in ec.cuh
+constexpr int U = T0, V = T0 + 1, W = T0 + 2, S = T0 + 3, XX = T0 + 4, M = T0 + 5, MM = T0 + 6, D = T0 + 7, YA = T0 + 8, YB = T0 + 9;
+__constant__ uint32_t DBL[8][4] = {
+    {ins(ADD, U, Y, Y), IDLE, IDLE, IDLE},
+    {ins(MUL, V, U, U), ins(MUL, XX, X, X), IDLE, IDLE},
+    {ins(TRIPLE, M, XX, XX), IDLE, IDLE, IDLE},
+    {ins(MUL, W, U, V), ins(MUL, S, X, V), ins(MUL, MM, M, M), ins(MUL, ZZ, V, ZZ)},
+    {ins(SUB2, X, MM, S), IDLE, IDLE, IDLE},
+    {ins(SUB, D, S, X), IDLE, IDLE, IDLE},
+    {ins(MUL, YA, M, D), ins(MUL, YB, W, Y), ins(MUL, ZZZ, W, ZZZ), IDLE},
+    {ins(SUB, Y, YA, YB), IDLE, IDLE, IDLE},
+};
+constexpr uint32_t DBL_MUL_STEPS = 0b01001010;
+// add-2008-s, see XYZZ::add in ec.cuh; part A ends with P = U2 - U1 (P == 0: doubling / inverse case, handled outside)
+constexpr int U1 = T0, U2 = T0 + 1, S1 = T0 + 2, S2 = T0 + 3, P = T0 + 4, R = T0 + 5, PP = T0 + 6, RR = T0 + 7, Z12 = T0 + 8, Z123 = T0 + 9,
+              PPP = T0 + 10, QQ = T0 + 11;
+__constant__ uint32_t ADDA[2][4] = {
+    {ins(MUL, U1, X, Q + 2), ins(MUL, U2, Q + 0, ZZ), ins(MUL, S1, Y, Q + 3), ins(MUL, S2, Q + 1, ZZZ)},
+    {ins(SUB, P, U2, U1), ins(SUB, R, S2, S1), IDLE, IDLE},
+};
+constexpr uint32_t ADDA_MUL_STEPS = 0b01;
+__constant__ uint32_t ADDB[7][4] = {
+    {ins(MUL, PP, P, P), ins(MUL, RR, R, R), ins(MUL, Z12, ZZ, Q + 2), ins(MUL, Z123, ZZZ, Q + 3)},
+    {ins(MUL, PPP, P, PP), ins(MUL, QQ, U1, PP), ins(MUL, ZZ, Z12, PP), IDLE},
+    {ins(SUB, X, RR, PPP), IDLE, IDLE, IDLE},
+    {ins(SUB2, X, X, QQ), IDLE, IDLE, IDLE},
+    {ins(SUB, U2, QQ, X), IDLE, IDLE, IDLE},
+    {ins(MUL, S2, R, U2), ins(MUL, S1, S1, PPP), ins(MUL, ZZZ, Z123, PPP), IDLE},
+    {ins(SUB, Y, S2, S1), IDLE, IDLE, IDLE},
+};
+constexpr uint32_t ADDB_MUL_STEPS = 0b0100011;
+
+__device__ __forceinline__ void run(const uint32_t (*prog)[4], int nsteps, uint32_t mul_steps, Fq *Rg, int qbase, int lane)
 {
-    __shared__ G1X tab[2][16];
-    const int p = blockIdx.x, which = threadIdx.x >> 5; // 0: s * g1_A, 1: r * g1_B
-    if (threadIdx.x & 31) return;
-    const Fr k = ld_vec(P + (size_t)p * zlen + (which == 0 ? nv + 2 : nv + 1));
-    G1X *T = tab[which];
-    const G1X base = ld_vec(rab + 2 * (size_t)p + which);
-    T[0] = G1X::inf();
-    T[1] = base;
-    for (int d = 2; d < 16; d++) {
-        G1X v = T[d >> 1];
-        v = v.dbl();
-        if (d & 1) v.add(base);
-        T[d] = v;
+    for (int s = 0; s < nsteps; s++) {
+        const uint32_t in = prog[s][lane];
+        int d = in & 0xff, a = (in >> 8) & 0xff, b = (in >> 16) & 0xff;
+        const int op = in >> 24;
+        if (a >= Q) a = qbase + (a - Q);
+        if (b >= Q) b = qbase + (b - Q);
+        if (op == NOP) d = DUMP + lane;
+        const Fq x = Rg[a], y = Rg[b];
+        Fq t;
+        if ((mul_steps >> s) & 1u) {
+            t = x * y;
+        } else {
+            const Fq sum = x + y, dif = x - y;
+            t = op == ADD ? sum : op == SUB ? dif : op == SUB2 ? dif - y : sum + x;
+        }
+        __syncwarp(0xfu); // every operand has been read (steps update registers in place)
+        Rg[d] = t;
+        __syncwarp(0xfu);
     }
-    G1X acc = G1X::inf();
-    for (int w = 63; w >= 0; w--) {
-        if (w != 63)
-            for (int i = 0; i < 4; i++) acc = acc.dbl();
-        const uint32_t d = (k.v[w >> 3] >> ((w & 7) * 4)) & 15u;
-        if (d) acc.add(T[d]);
+}
+} // namespace vm
+
+__global__ void __launch_bounds__(64)
+k_smul(const G1X *__restrict__ rab, const Fr *__restrict__ Pl, size_t zlen, size_t nv, G1X *__restrict__ sm)
+{
+    __shared__ Fq regs[2][96];
+    const int p = blockIdx.x, which = threadIdx.x >> 5, lane = threadIdx.x & 31; // 0: s * g1_A, 1: r * g1_B
+    if (lane >= 4) return;
+    Fq *Rg = regs[which];
+    const Fr k = ld_vec(Pl + (size_t)p * zlen + (which == 0 ? nv + 2 : nv + 1));
+    const G1X *src = rab + 2 * (size_t)p + which;
+    G1X *dst = sm + 2 * (size_t)p + which;
+    const Fq *srcw = reinterpret_cast<const Fq *>(src);
+    // lane c owns coordinate c of every point copy
+    auto copy = [&](int to, int from) {
+        const Fq v = Rg[from + lane];
+        __syncwarp(0xfu);
+        Rg[to + lane] = v;
+        __syncwarp(0xfu);
+    };
+    Rg[32 + 4 + lane] = ld_vec(srcw + lane); // T[1] = base
+    __syncwarp(0xfu);
+    const bool base_inf = Rg[32 + 4 + vm::ZZ].is_zero();
+    bool fallback = false;
+    if (!base_inf) {
+        for (int d = 2; d < 16; d++) { // T[d] = 2 T[d / 2] (+ T[1])
+            copy(vm::X, 32 + 4 * (d >> 1));
+            vm::run(vm::DBL, 8, vm::DBL_MUL_STEPS, Rg, 0, lane);
+            if (d & 1) {
+                vm::run(vm::ADDA, 2, vm::ADDA_MUL_STEPS, Rg, 32 + 4, lane);
+                fallback |= Rg[vm::P].is_zero();
+                vm::run(vm::ADDB, 7, vm::ADDB_MUL_STEPS, Rg, 32 + 4, lane);
+            }
+            copy(32 + 4 * d, vm::X);
+        }
+        bool acc_inf = true;
+        for (int w = 63; w >= 0; w--) {
+            if (!acc_inf)
+                for (int i = 0; i < 4; i++) vm::run(vm::DBL, 8, vm::DBL_MUL_STEPS, Rg, 0, lane);
+            const int d = (int)((k.v[w >> 3] >> ((w & 7) * 4)) & 15u);
+            if (!d) continue;
+            if (acc_inf) {
+                copy(vm::X, 32 + 4 * d);
+                acc_inf = false;
+                continue;
+            }
+            vm::run(vm::ADDA, 2, vm::ADDA_MUL_STEPS, Rg, 32 + 4 * d, lane);
+            fallback |= Rg[vm::P].is_zero(); // 16 m P == +- d P cannot happen for m < r / 16; guarded all the same
+            vm::run(vm::ADDB, 7, vm::ADDB_MUL_STEPS, Rg, 32 + 4 * d, lane);
+        }
+        if (acc_inf) { // k == 0
+            Rg[lane] = Fq::zero();
+            __syncwarp(0xfu);
+        }
     }
-    st_vec(sm + 2 * (size_t)p + which, acc);
+    if (base_inf || fallback) {
+        if (lane == 0) st_vec(dst, base_inf ? G1X::inf() : scalar_mul<Fq>(k.v, ld_vec(src)));
+        return;
+    }
+    st_vec(reinterpret_cast<Fq *>(dst) + lane, Rg[lane]);
 }
 
 // g1_C = job C + s * g1_A + r * g1_B (r1cs_gg_ppzksnark.tcc:495); proof = (g1_A, g2_B, g1_C) as Jacobian limbs
@@ -259,6 +409,18 @@ int upload_csr(zkb_ctx *ctx, zkb_key *key, int mat, const zkb_csr &h)
             perm[cnt[maxlen - len]++] = (uint32_t)i;
             if (len >= (uint32_t)SPMV_LONG) key->nlong[mat]++;
         }
+        key->ngiant[mat] = 0;
+        for (size_t k = 0; k < nc && rp[perm[k] + 1] - rp[perm[k]] >= (uint32_t)SPMV_GIANT; k++) {
+            const uint32_t row = perm[k], lo = rp[row], hi = rp[row + 1];
+            const uint32_t first = (uint32_t)(key->h_giant_seg.size() / 4);
+            for (uint32_t e = lo; e < hi; e += SPMV_GIANT_SEG) {
+                const uint32_t v[4] = {(uint32_t)mat, row, e, std::min(hi, e + (uint32_t)SPMV_GIANT_SEG)};
+                key->h_giant_seg.insert(key->h_giant_seg.end(), v, v + 4);
+            }
+            const uint32_t r[4] = {(uint32_t)mat, row, first, (uint32_t)(key->h_giant_seg.size() / 4) - first};
+            key->h_giant_row.insert(key->h_giant_row.end(), r, r + 4);
+            key->ngiant[mat]++;
+        }
         ZKB_CUDA(ctx, cudaMalloc(&key->rowperm[mat], (nc + 1) * 4));
         ZKB_CUDA(ctx, cudaMemcpy(key->rowperm[mat], perm.data(), nc * 4, cudaMemcpyHostToDevice));
         key->bytes += (nc + 1) * 4;
@@ -280,6 +442,8 @@ void key_release(zkb_key *key)
     for (int k = 0; k < 3; k++) {
         if (key->rowptr[k]) cudaFree(key->rowptr[k]);
         if (key->rowperm[k]) cudaFree(key->rowperm[k]);
+        if (k == 0 && key->giant_seg) cudaFree(key->giant_seg);
+        if (k == 0 && key->giant_row) cudaFree(key->giant_row);
         if (key->col[k]) cudaFree(key->col[k]);
         if (key->coeff[k]) cudaFree(key->coeff[k]);
     }
@@ -312,6 +476,15 @@ int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key)
     const zkb_csr *mats[3] = {&d->A, &d->B, &d->C};
     for (int k = 0; k < 3; k++)
         if ((rc = upload_csr(ctx, key, k, *mats[k]))) return rc;
+    key->n_giant_seg = (uint32_t)(key->h_giant_seg.size() / 4);
+    key->n_giant_row = (uint32_t)(key->h_giant_row.size() / 4);
+    if (key->n_giant_row) {
+        ZKB_CUDA(ctx, cudaMalloc(&key->giant_seg, key->h_giant_seg.size() * 4));
+        ZKB_CUDA(ctx, cudaMalloc(&key->giant_row, key->h_giant_row.size() * 4));
+        ZKB_CUDA(ctx, cudaMemcpy(key->giant_seg, key->h_giant_seg.data(), key->h_giant_seg.size() * 4, cudaMemcpyHostToDevice));
+        ZKB_CUDA(ctx, cudaMemcpy(key->giant_row, key->h_giant_row.data(), key->h_giant_row.size() * 4, cudaMemcpyHostToDevice));
+        key->bytes += (key->h_giant_seg.size() + key->h_giant_row.size()) * 4;
+    }
     key->zlen = (nv + 4 + m + 1 + 3) & ~(size_t)3;
     key->nnzB = d->B_nnz;
 
@@ -452,6 +625,15 @@ int witness_map_chunk(zkb_ctx *ctx, const zkb_key *key, int batch, uint32_t *d_f
         csr.coeff[k] = key->coeff[k];
         csr.perm[k] = key->rowperm[k];
         csr.nlong[k] = key->nlong[k];
+        csr.ngiant[k] = key->ngiant[k];
+    }
+    if (key->n_giant_row) {
+        ZKB_CUDA(ctx, ctx->scratch[SP_GIANT].ensure((size_t)batch * key->n_giant_seg * sizeof(Fr)));
+        Fr *partial = ctx->scratch[SP_GIANT].as<Fr>();
+        k_spmv_giant<<<dim3(key->n_giant_seg, batch), 128, 0, st>>>(csr, key->giant_seg, Z, key->zlen, key->n_giant_seg, partial);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_spmv_giant_finish<<<dim3(key->n_giant_row, batch), 32, 0, st>>>(key->giant_row, partial, key->n_giant_seg, m, batch, abc);
+        ZKB_LAUNCH_CHECK(ctx);
     }
     const uint32_t long_blocks = (std::max(key->nlong[0], std::max(key->nlong[1], key->nlong[2])) + 3) / 4;
     k_spmv<<<dim3(long_blocks + ceil_div(m, 128), 3, batch), 128, 0, st>>>(csr, long_blocks, Z, key->zlen, key->nc, key->ni, m, batch, abc);
