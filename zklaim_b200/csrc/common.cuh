@@ -69,7 +69,7 @@ namespace zkb {
 // scratch slots of a context.  An MSM run owns one "lane" of slots; the prover runs three lanes concurrently
 // (G1 job C on the main stream, G1 jobs A + B1 and the G2 job on the side streams)
 enum {
-    SB_HIST = 0, SB_START, SB_CURSOR, SB_BLOCKSUM, SB_ENT, SB_EBKT, SB_PARTS, SB_BUCKETS, SB_L1, SB_L2, SB_RES, SB_WIDE,
+    SB_HIST = 0, SB_START, SB_CURSOR, SB_BLOCKSUM, SB_ENT, SB_EBKT, SB_PARTS, SB_BUCKETS, SB_L1, SB_L2, SB_RES, SB_WIDE, SB_WIDESUM,
     SB_PER_GROUP,                      // slots above are per lane: index + msm_slot(ctx, group)
     SB_SCAL = 3 * SB_PER_GROUP, SB_PLAIN, SB_STAGE_A, SB_STAGE_B, SB_STAGE_O, SB_MISC,
     SB_PROVER0 // first slot of prover.cu

@@ -24,12 +24,13 @@ template <class PT> __device__ __forceinline__ PT sm_get(const uint32_t *sm, int
 // One lane per bucket for short spans, the whole warp for medium spans; a bucket that spans very many runs
 // (the "scalar == 1" bucket of a Groth16 witness holds thousands of pairs) is queued for k_fixup_wide, where a
 // whole thread block reduces it.
-constexpr int FIXUP_WIDE_T = 256; // threads of a k_fixup_wide block
+constexpr int FIXUP_WIDE_T = 256;  // threads of a k_fixup_wide block
+constexpr int FIXUP_CHUNK = 1024;  // runs per block there: a bucket of the "scalar == 1" kind spans 10^5 runs at 2^22 constraints
 constexpr int FIXUP_T = 128, FIXUP_WARP = 8, FIXUP_BLOCK = 64;
 template <class F>
 __global__ void __launch_bounds__(FIXUP_T)
 k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *__restrict__ buckets,
-        const XYZZ<F> *__restrict__ parts, uint32_t *__restrict__ wide_list)
+        const XYZZ<F> *__restrict__ parts, uint32_t *__restrict__ wide_list, uint32_t max_chunks)
 {
     extern __shared__ uint32_t sm[];
     const uint32_t S = msm_run_length(start[B], rmax);
@@ -59,7 +60,18 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *
     const bool medium = multi && !block_wide && (t1 - t0) >= FIXUP_WARP;
     const int n_medium = __popc(__ballot_sync(0xffffffffu, medium));
     const bool wide = medium && n_medium <= 4;
-    if (block_wide) wide_list[1 + atomicAdd(wide_list, 1u)] = b;
+    if (block_wide) { // queue layout: [0] chunk count, [1] bucket count, chunks (b, index), bucket records (b, first chunk, chunks)
+        const uint32_t n = (t1 - t0 + FIXUP_CHUNK) / FIXUP_CHUNK;
+        const uint32_t first = atomicAdd(wide_list, n), rec = atomicAdd(wide_list + 1, 1u);
+        uint32_t *chunks = wide_list + 2, *recs = wide_list + 2 + 2 * (size_t)max_chunks;
+        recs[3 * rec] = b;
+        recs[3 * rec + 1] = first;
+        recs[3 * rec + 2] = n;
+        for (uint32_t i = 0; i < n; i++) {
+            chunks[2 * (first + i)] = b;
+            chunks[2 * (first + i) + 1] = i;
+        }
+    }
     if (multi && !wide && !block_wide) {
         XYZZ<F> acc = ld_vec(parts + 2 * (size_t)t0 + ((s == t0 * S) ? 0 : 1));
         for (uint32_t t = t0 + 1; t <= t1; t++) acc.add(ld_vec(parts + 2 * (size_t)t));
@@ -92,25 +104,59 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *
     }
 }
 
-// the queued buckets, one thread block each (grid-stride over the queue)
+// the queued buckets: a block per chunk of FIXUP_CHUNK runs (grid-stride over the chunk queue) ...
 template <class F>
 __global__ void __launch_bounds__(FIXUP_WIDE_T)
-k_fixup_wide(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *__restrict__ buckets,
-             const XYZZ<F> *__restrict__ parts, const uint32_t *__restrict__ wide_list)
+k_fixup_wide(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, const XYZZ<F> *__restrict__ parts,
+             const uint32_t *__restrict__ wide_list, XYZZ<F> *__restrict__ chunk_sums)
 {
     extern __shared__ uint32_t sm[];
     const uint32_t S = msm_run_length(start[B], rmax);
     const int T = blockDim.x, t = threadIdx.x;
     const uint32_t count = wide_list[0];
+    const uint32_t *chunks = wide_list + 2;
     for (uint32_t i = blockIdx.x; i < count; i += gridDim.x) {
-        const uint32_t b = wide_list[1 + i];
+        const uint32_t b = chunks[2 * i], ch = chunks[2 * i + 1];
         const uint32_t s = start[b], e = start[b + 1];
         const uint32_t t0 = s / S, t1 = (e - 1) / S;
+        const uint32_t lo = t0 + ch * FIXUP_CHUNK;
+        const uint32_t hi = (t1 - lo >= (uint32_t)FIXUP_CHUNK) ? lo + FIXUP_CHUNK - 1 : t1;
         XYZZ<F> acc = XYZZ<F>::inf();
-        for (uint32_t r = t0 + t; r <= t1; r += T) {
+        for (uint32_t r = lo + t; r <= hi; r += T) {
             const size_t idx = (r == t0) ? 2 * (size_t)r + ((s == r * S) ? 0 : 1) : 2 * (size_t)r;
             acc.add(ld_vec(parts + idx));
         }
+        sm_put(sm, T, t, acc);
+        __syncthreads();
+        for (int d = T >> 1; d > 0; d >>= 1) {
+            if (t < d) {
+                acc.add(sm_get<XYZZ<F>>(sm, T, t + d));
+                sm_put(sm, T, t, acc);
+            }
+            __syncthreads();
+        }
+        if (t == 0) st_vec(chunk_sums + i, acc);
+        __syncthreads();
+    }
+}
+// ... then a block per queued bucket adds up its chunk sums
+template <class F>
+__global__ void __launch_bounds__(128)
+k_fixup_wide_sum(XYZZ<F> *__restrict__ buckets, const uint32_t *__restrict__ wide_list, uint32_t max_chunks,
+                 const XYZZ<F> *__restrict__ chunk_sums)
+{
+    extern __shared__ uint32_t sm[];
+    const int T = blockDim.x, t = threadIdx.x;
+    const uint32_t count = wide_list[1];
+    const uint32_t *recs = wide_list + 2 + 2 * (size_t)max_chunks;
+    for (uint32_t i = blockIdx.x; i < count; i += gridDim.x) {
+        const uint32_t b = recs[3 * i], first = recs[3 * i + 1], n = recs[3 * i + 2];
+        if (n == 1) {
+            if (t == 0) st_vec(buckets + b, ld_vec(chunk_sums + first));
+            continue;
+        }
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (uint32_t k = t; k < n; k += T) acc.add(ld_vec(chunk_sums + first + k));
         sm_put(sm, T, t, acc);
         __syncthreads();
         for (int d = T >> 1; d > 0; d >>= 1) {
@@ -276,12 +322,15 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
     uint32_t *start = ctx->scratch[gs + SB_START].as<uint32_t>();
     PT *parts = ctx->scratch[gs + SB_PARTS].as<PT>();
     PT *buckets = ctx->scratch[gs + SB_BUCKETS].as<PT>();
-    // queue of buckets for the block-wide fix-up: a bucket enters it when it spans >= FIXUP_BLOCK runs
-    const size_t max_wide = (size_t)rmax / (FIXUP_BLOCK / 2) + 16; // a queued bucket owns >= FIXUP_BLOCK - 1 runs
-    ZKB_CUDA(ctx, ctx->scratch[gs + SB_WIDE].ensure((max_wide + 1) * 4));
+    // queue for the block-wide fix-up: a bucket enters it when it spans >= FIXUP_BLOCK runs (so it owns at least
+    // FIXUP_BLOCK - 1 of the rmax runs), as ceil(span / FIXUP_CHUNK) chunks
+    const uint32_t max_wide = rmax / (FIXUP_BLOCK / 2) + 16, max_chunks = max_wide + rmax / FIXUP_CHUNK + 16;
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_WIDE].ensure((2 + 2 * (size_t)max_chunks + 3 * (size_t)max_wide) * 4));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_WIDESUM].ensure((size_t)max_chunks * sizeof(PT)));
     uint32_t *wide = ctx->scratch[gs + SB_WIDE].as<uint32_t>();
-    ZKB_CUDA(ctx, cudaMemsetAsync(wide, 0, 4, st));
-    k_fixup<F><<<ceil_div(B, FIXUP_T), FIXUP_T, (FIXUP_T / 32) * 32 * sizeof(PT), st>>>(start, (uint32_t)B, rmax, buckets, parts, wide);
+    PT *chunk_sums = ctx->scratch[gs + SB_WIDESUM].as<PT>();
+    ZKB_CUDA(ctx, cudaMemsetAsync(wide, 0, 8, st));
+    k_fixup<F><<<ceil_div(B, FIXUP_T), FIXUP_T, (FIXUP_T / 32) * 32 * sizeof(PT), st>>>(start, (uint32_t)B, rmax, buckets, parts, wide, max_chunks);
     ZKB_LAUNCH_CHECK(ctx);
     {
         const uint32_t attr_bit = plan->group == ZKB_G2 ? 4u : 2u; // function attributes are per device = per context
@@ -289,8 +338,9 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
             ZKB_CUDA(ctx, cudaFuncSetAttribute(k_fixup_wide<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FIXUP_WIDE_T * sizeof(PT))));
             ctx->func_attr_done |= attr_bit;
         }
-        size_t wblocks = max_wide < (size_t)ctx->sm_count * 2 ? max_wide : (size_t)ctx->sm_count * 2;
-        k_fixup_wide<F><<<(unsigned)wblocks, FIXUP_WIDE_T, FIXUP_WIDE_T * sizeof(PT), st>>>(start, (uint32_t)B, rmax, buckets, parts, wide);
+        k_fixup_wide<F><<<(unsigned)ctx->sm_count * 2, FIXUP_WIDE_T, FIXUP_WIDE_T * sizeof(PT), st>>>(start, (uint32_t)B, rmax, parts, wide, chunk_sums);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_fixup_wide_sum<F><<<(unsigned)ctx->sm_count, 128, 128 * sizeof(PT), st>>>(buckets, wide, max_chunks, chunk_sums);
         ZKB_LAUNCH_CHECK(ctx);
     }
     for (uint32_t q = 0; q < tab.njobs; q++) {
