@@ -51,8 +51,10 @@ CachedKey &key_for_ctx(zklaim_ctx *ctx)
     return g_keys_by_pk_hash[h] = ck;
 }
 
-/* host half of generate_proof (snark.cpp:113-124): circuit + witness from the credential; false = unsatisfied */
-bool build_witness(zklaim_ctx *ctx, std::vector<FrT> &primary, std::vector<FrT> &auxiliary)
+/* host half of generate_proof exactly as the reference runs it (snark.cpp:113-124): circuit + constraints + witness +
+ * host-side satisfiability check per proof; false = unsatisfied.  ~110 ms per 1-payload credential on one core, of
+ * which 10 ms are the witness.  Used when ZKB_HOST_CHECK=1. */
+bool build_witness_reference(zklaim_ctx *ctx, std::vector<FrT> &primary, std::vector<FrT> &auxiliary)
 {
     protoboard<FrT> pb;
     zklaim_gadget<FrT> g(pb, ctx);
@@ -61,6 +63,53 @@ bool build_witness(zklaim_ctx *ctx, std::vector<FrT> &primary, std::vector<FrT> 
     if (!pb.is_satisfied()) return false;
     primary = pb.primary_input();
     auxiliary = pb.auxiliary_input();
+    return true;
+}
+
+/* the circuit's shape depends on the payload count only (zklaim_gadget.cpp:348-540 walks
+ * the chain, predicates and values are witness data), constraint generation is not needed to compute the witness
+ * (zklaim_gadget.cpp:705-783 only assigns values), and the GPU prover checks <a,z><b,z> = <c,z> for every constraint
+ * itself (k_sat_check -> ZKB_ERR_UNSAT).  So a gadget is built once per payload count and thread and re-witnessed per
+ * credential: ~10 ms instead of ~110 ms per proof, and credentials of a batch are processed by all host threads. */
+struct WitnessEngine {
+    std::vector<zklaim_wrap_payload_ctx> proto;
+    zklaim_ctx pctx;
+    protoboard<FrT> pb;
+    std::unique_ptr<zklaim_gadget<FrT>> g;
+    explicit WitnessEngine(size_t k) : proto(k)
+    {
+        memset(&pctx, 0, sizeof(pctx));
+        for (size_t i = 0; i < k; i++) {
+            memset(&proto[i].pl, 0, sizeof(proto[i].pl));
+            proto[i].next = i + 1 < k ? &proto[i + 1] : NULL;
+        }
+        pctx.num_of_payloads = k;
+        pctx.pl_ctx_head = k ? &proto[0] : NULL;
+        g.reset(new zklaim_gadget<FrT>(pb, &pctx));
+    }
+    void run(zklaim_ctx *ctx, std::vector<FrT> &primary, std::vector<FrT> &auxiliary)
+    {
+        pb.clear_values(); /* a fresh protoboard starts from zeros (protoboard.tcc) */
+        g->generate_r1cs_witness(ctx);
+        primary = pb.primary_input();
+        auxiliary = pb.auxiliary_input();
+    }
+};
+
+bool host_check_enabled()
+{
+    const char *e = getenv("ZKB_HOST_CHECK");
+    return e && atoi(e) != 0;
+}
+
+/* witness of one credential; false = the reference's host-side check (if enabled) found it unsatisfied */
+bool build_witness(zklaim_ctx *ctx, std::vector<FrT> &primary, std::vector<FrT> &auxiliary)
+{
+    if (host_check_enabled()) return build_witness_reference(ctx, primary, auxiliary);
+    static thread_local std::map<size_t, std::unique_ptr<WitnessEngine>> engines;
+    std::unique_ptr<WitnessEngine> &e = engines[ctx->num_of_payloads];
+    if (!e) e.reset(new WitnessEngine(ctx->num_of_payloads));
+    e->run(ctx, primary, auxiliary);
     return true;
 }
 
@@ -73,10 +122,12 @@ struct StdoutMute { /* what libsnark_wrapper.cpp:221-226 / :245-246 do around ev
         saved = dup(STDOUT_FILENO);
         fflush(stdout);
         close(STDOUT_FILENO);
+        std::cout.setstate(std::ios_base::failbit); /* the gadget streams every witness value to cout (:770, :781) */
     }
     ~StdoutMute()
     {
         fflush(stdout);
+        std::cout.clear();
         dup2(saved, STDOUT_FILENO);
         close(saved);
     }
@@ -96,8 +147,18 @@ int zkb_libsnark_prove(zklaim_ctx *ctx)
         std::vector<FrT> primary, auxiliary;
         if (!build_witness(ctx, primary, auxiliary)) return 1;
         const FrT r = FrT::random_element(), s = FrT::random_element();
-        const r1cs_gg_ppzksnark_proof<ppT> proof = prover_with_rs(ck.key, primary, auxiliary, r, s);
-        ctx->proof_size = libsnark_export_proof(proof, &ctx->proof);
+        std::vector<uint64_t> w(4 * (primary.size() + auxiliary.size()));
+        pack_assignment(primary, auxiliary, w.data());
+        Session::get().tune_once(ck.key, w.data());
+        zkb_proof out;
+        zkb_ctx *z = Session::get().ctx();
+        const int rc = zkb_prove(z, ck.key, w.data(), (const uint64_t *)r.mont_repr.data, (const uint64_t *)s.mont_repr.data, &out, NULL);
+        if (rc == ZKB_ERR_UNSAT) return 1; /* libsnark_wrapper.cpp:233-240: witness unsatisfied */
+        if (rc != ZKB_OK) {
+            fprintf(stderr, "zkb_prove: %s\n", zkb_last_error(z));
+            return -1;
+        }
+        ctx->proof_size = libsnark_export_proof(wrap_proof(out), &ctx->proof);
         return 0;
     } catch (const std::exception &e) {
         fprintf(stderr, "zkb_libsnark_prove: %s\n", e.what());
@@ -115,18 +176,33 @@ int zkb_libsnark_prove_batch(zklaim_ctx **ctxs, size_t n)
         CachedKey &ck = key_for_ctx(ctxs[0]);
         const size_t nv = ck.num_variables;
         std::vector<uint64_t> w(n * nv * 4), r(n * 4), s(n * 4);
+        int bad = 0;
+#pragma omp parallel for schedule(dynamic, 1)
         for (size_t i = 0; i < n; i++) {
             std::vector<FrT> primary, auxiliary;
-            if (!build_witness(ctxs[i], primary, auxiliary)) return 1;
-            if (primary.size() + auxiliary.size() != nv) return -2;
+            if (!build_witness(ctxs[i], primary, auxiliary)) {
+#pragma omp atomic write
+                bad = 1;
+                continue;
+            }
+            if (primary.size() + auxiliary.size() != nv) {
+#pragma omp atomic write
+                bad = 2;
+                continue;
+            }
             pack_assignment(primary, auxiliary, &w[i * nv * 4]);
+        }
+        if (bad) return bad == 1 ? 1 : -2;
+        for (size_t i = 0; i < n; i++) {
             put_fr(&r[4 * i], FrT::random_element());
             put_fr(&s[4 * i], FrT::random_element());
         }
         Session::get().tune_once(ck.key, w.data());
         std::vector<zkb_proof> out(n);
         zkb_ctx *z = Session::get().ctx();
-        if (zkb_prove_batch(z, ck.key, n, w.data(), r.data(), s.data(), out.data()) != ZKB_OK) {
+        const int rc = zkb_prove_batch(z, ck.key, n, w.data(), r.data(), s.data(), out.data());
+        if (rc == ZKB_ERR_UNSAT) return 1;
+        if (rc != ZKB_OK) {
             fprintf(stderr, "zkb_prove_batch: %s\n", zkb_last_error(z));
             return -1;
         }
@@ -255,14 +331,20 @@ int zkbr_witnesses(void *h, size_t count, uint64_t seed0, uint64_t *w_out)
     StdoutMute mute;
     ppT::init_public_params();
     const size_t nv = b->key.num_variables;
+    int bad = 0;
+#pragma omp parallel for schedule(dynamic, 1)
     for (size_t i = 0; i < count; i++) {
         Credential c(b->payloads, seed0 + i);
         std::vector<FrT> primary, auxiliary;
-        if (!build_witness(&c.ctx, primary, auxiliary)) return 1;
-        if (primary.size() + auxiliary.size() != nv) return 2;
+        if (!build_witness(&c.ctx, primary, auxiliary) || primary.size() + auxiliary.size() != nv) {
+#pragma omp atomic write
+            bad = 1;
+            continue;
+        }
         pack_assignment(primary, auxiliary, w_out + i * nv * 4);
-        if (i == 0) Session::get().tune_once(b->key.key, w_out);
     }
+    if (bad) return bad;
+    Session::get().tune_once(b->key.key, w_out);
     return 0;
 }
 
@@ -285,6 +367,19 @@ int zkbr_verify(void *h, const uint64_t *w, const zkb_proof *proof)
     std::vector<FrT> primary(b->key.num_inputs);
     for (size_t i = 0; i < primary.size(); i++) memcpy(primary[i].mont_repr.data, w + 4 * i, 32);
     return r1cs_gg_ppzksnark_verifier_strong_IC<ppT>(vk, primary, wrap_proof(*proof)) ? 1 : 0;
+}
+
+/* a credential whose commitment does not match its pre-image (one hash byte flipped) through zkb_libsnark_prove:
+ * the reference returns 1 for it (libsnark_wrapper.cpp:233-240); so must the GPU path (k_sat_check -> ZKB_ERR_UNSAT) */
+int zkbr_prove_tampered(void *h, uint64_t seed)
+{
+    Bench *b = (Bench *)h;
+    Credential c(b->payloads, seed);
+    c.chain[0].pl.hash[3] ^= 0x40;
+    c.ctx.pk_size = b->issuer->ctx.pk_size;
+    c.ctx.pk = (unsigned char *)malloc(c.ctx.pk_size);
+    memcpy(c.ctx.pk, b->issuer->ctx.pk, c.ctx.pk_size);
+    return zkb_libsnark_prove(&c.ctx);
 }
 
 /* end to end through the zklaim-facing entry points: `count` credentials -> zkb_libsnark_prove_batch ->

@@ -1,0 +1,50 @@
+"""The zklaim-facing side of the drop-in (bridge/zkb_zklaim_bridge.cpp): credentials -> zkb_libsnark_prove(_batch) ->
+the reference's own libsnark_verify; the cached, constraint-free witness engine against the
+reference's per-proof pipeline; the reference's return-code contract for an unsatisfied credential."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cred():
+    from zklaim_b200 import bridge
+    if not bridge.available():
+        pytest.skip("bridge/_build/libzkb_zklaim.so not built (make -C bridge, needs the reference tree)")
+    c = bridge.Credentials(1, seed=3)
+    yield c
+    c.close()
+
+
+def test_roundtrip_through_the_zklaim_entry_points(cred):
+    ok, t_prove, t_verify = cred.roundtrip(1, 4000)
+    assert ok == 1
+    ok, t_prove, t_verify = cred.roundtrip(6, 4100)
+    assert ok == 6
+
+
+def test_cached_witness_engine_equals_reference_pipeline(cred):
+    """the engine skips generate_r1cs_constraints / is_satisfied and re-uses one gadget per thread: the assignment must
+    be the one the reference's snark.cpp:113-124 computes (ZKB_HOST_CHECK=1 selects that pipeline in the bridge)"""
+    fast = cred.witnesses(5, 8000)
+    os.environ["ZKB_HOST_CHECK"] = "1"
+    try:
+        slow = cred.witnesses(5, 8000)
+    finally:
+        del os.environ["ZKB_HOST_CHECK"]
+    assert np.array_equal(fast, slow)
+    assert not np.array_equal(fast[0], fast[1])
+
+
+def test_unsatisfied_credential_returns_one(cred):
+    assert cred.prove_tampered(91) == 1
+    os.environ["ZKB_HOST_CHECK"] = "1"
+    try:
+        assert cred.prove_tampered(92) == 1
+    finally:
+        del os.environ["ZKB_HOST_CHECK"]
+    ok, _, _ = cred.roundtrip(2, 4200)  # the session is still healthy afterwards
+    assert ok == 2

@@ -29,6 +29,7 @@ _SIG = {
     "zkbr_random_fr": (None, [_sz, _vp]),
     "zkbr_verify": (_i, [_vp, _vp, _vp]),
     "zkbr_roundtrip": (_i, [_vp, _sz, _u64, _vp]),
+    "zkbr_prove_tampered": (_i, [_vp, _u64]),
 }
 _lib = None
 
@@ -92,6 +93,10 @@ class Credentials:
         t = (C.c_double * 2)()
         ok = self.L.zkbr_roundtrip(self.h, count, seed0, t)
         return ok, t[0], t[1]
+
+    def prove_tampered(self, seed: int = 77) -> int:
+        """zkb_libsnark_prove on a credential whose hash was tampered with: the reference's contract says 1"""
+        return int(self.L.zkbr_prove_tampered(self.h, seed))
 
     def close(self):
         if self.h:
