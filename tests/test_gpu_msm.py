@@ -17,7 +17,7 @@ def _check(ref, group, got, exp):
 
 
 @pytest.mark.parametrize("n,c,pf", [(1, 0, 0), (7, 4, 1), (300, 5, 1), (300, 6, 0), (5000, 0, 1), (5000, 0, 0),
-                                    (5000, 9, 3), (40000, 0, 0)])
+                                    (5000, 9, 3), (40000, 0, 0), (40000, 18, 0), (3000, 20, 2)])
 def test_g1_msm_matches_reference(zctx, ref, n, c, pf):
     bases = ref.bases(zk.G1, 1 << 40, n)
     s = ref.sha512_rng(77 << 32, n)

@@ -229,7 +229,7 @@ int msm_choose_c(size_t n_eff, int group, int precompute_factor)
     const double madd = group == ZKB_G2 ? 30 : 10, add = group == ZKB_G2 ? 42 : 14, dbl = group == ZKB_G2 ? 27 : 9;
     int best = 4;
     double best_cost = 1e300;
-    for (int c = 4; c <= 16; c++) {
+    for (int c = 4; c <= MSM_MAX_C; c++) {
         const int W = (255 + c - 1) / c;
         int F = precompute_factor <= 0 ? W : precompute_factor;
         if (F > W) F = W;
@@ -249,7 +249,7 @@ int plan_add_job(zkb_ctx *ctx, MsmPlan *plan, size_t n_total, int c, int precomp
 {
     JobTab &t = plan->tab;
     if (t.njobs >= MSM_MAX_JOBS) return fail(ctx, ZKB_ERR_ARG, "msm plan: too many jobs");
-    if (c < 2 || c > 16) return fail(ctx, ZKB_ERR_ARG, "msm plan: window bits must be 2..16");
+    if (c < 2 || c > MSM_MAX_C) return fail(ctx, ZKB_ERR_ARG, "msm plan: window bits must be 2..20");
     MsmJob &J = t.j[t.njobs];
     const int W = (255 + c - 1) / c;
     int F = precompute_factor <= 0 ? W : precompute_factor;
@@ -384,8 +384,8 @@ int zkb_bases_upload(zkb_ctx *ctx, int group, const uint64_t *affine, size_t n, 
 {
     if (!ctx || !affine || !out || n == 0 || (group != ZKB_G1 && group != ZKB_G2))
         return fail(ctx, ZKB_ERR_ARG, "zkb_bases_upload: bad argument");
-    if (window_bits < 0 || window_bits > 16 || window_bits == 1 || precompute_factor < 0)
-        return fail(ctx, ZKB_ERR_ARG, "zkb_bases_upload: window_bits must be 0 or 2..16");
+    if (window_bits < 0 || window_bits > MSM_MAX_C || window_bits == 1 || precompute_factor < 0)
+        return fail(ctx, ZKB_ERR_ARG, "zkb_bases_upload: window_bits must be 0 or 2..20");
     ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
     zkb_bases *b = new zkb_bases();
     b->plan.group = group;

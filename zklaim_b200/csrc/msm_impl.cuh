@@ -17,6 +17,7 @@ struct MsmJob {
 };
 
 constexpr int MSM_MAX_JOBS = 4;
+constexpr int MSM_MAX_C = 20; // widest window: 2^19 buckets per set
 
 struct JobTab {
     uint32_t njobs, n_items, Bp, pad; // Bp = buckets of one proof (all jobs, all sets)
