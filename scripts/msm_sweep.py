@@ -32,7 +32,8 @@ for lg in logs:
     rng = np.random.default_rng(lg + lo)
     u = rng.random(hi - lo)
     like = dense.copy(); like[u < 0.52] = 0; like[(u >= 0.52) & (u < 0.97)] = ONE_R
-    for name, sc in (("dense", dense), ("zklaim-like", like)):
+    for name, sc_host in (("dense", dense), ("zklaim-like", like)):
+        sc = torch.from_numpy(sc_host.view(np.int64)).cuda()   # scalars resident in HBM: the timed region is the MSM + gather
         best = 1e9
         for it in range(4):
             if world > 1:

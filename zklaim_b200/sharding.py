@@ -59,9 +59,12 @@ def sharded_msm(ctx, group_id: int, bases_local, scalars_local: np.ndarray, grou
     `combine(group_id, partials)` defaults to the GPU (ctx.group_sum)."""
     if group_id not in (G1, G2):
         raise ValueError("group_id must be G1 or G2")
-    if len(scalars_local):
-        part = ctx.msm(bases_local, scalars_local)
-    else:  # an empty range contributes the zero of the group, (0, 1, 0) in Montgomery form (alt_bn128_init.cpp:145-147)
+    if hasattr(scalars_local, "data_ptr"):  # a CUDA tensor of n x 4 int64 / uint64 limbs already on this rank's GPU
+        n = int(scalars_local.shape[0])
+        part = ctx.msm_device(bases_local, scalars_local.data_ptr(), n) if n else None
+    else:
+        part = ctx.msm(bases_local, scalars_local) if len(scalars_local) else None
+    if part is None:  # an empty range contributes the zero of the group, (0, 1, 0) in Montgomery form (alt_bn128_init.cpp:145-147)
         part = ctx.group_sum(group_id, np.zeros((0, 12 if group_id == G1 else 24), dtype=np.uint64))
     parts = gather_partials(part, group, device)
     return (combine or ctx.group_sum)(group_id, parts)
