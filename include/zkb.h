@@ -180,6 +180,25 @@ typedef struct {
 int zkb_prove(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4],
               zkb_proof *out, uint64_t *H_out);
 
+/* ---- one proof over several GPUs ------------------------------------------------------
+ * The five MSMs of a proof shard the way libff::multi_exp already chunks them on the CPU (multiexp.tcc:417-438):
+ * shard `rank` of `world` keeps the contiguous range [rank * n / world, ...) of the A, B, H and L queries (rank 0
+ * also the fixed elements alpha, beta, delta), every shard computes the witness map itself (replicas: no NTT is
+ * distributed) and its share of the four sums; the 480-byte shares are gathered (host / NCCL all_gather) and
+ * zkb_prove_combine adds them up and performs the assembly of r1cs_gg_ppzksnark.tcc:487-495. */
+typedef struct {
+    uint64_t A[12];  /* share of g1_A            (G1 Jacobian) */
+    uint64_t B1[12]; /* share of g1_B                          */
+    uint64_t C[12];  /* share of H + L - rs delta              */
+    uint64_t B2[24]; /* share of g2_B            (G2 Jacobian) */
+} zkb_partial;
+/* `desc` describes the WHOLE key (as for zkb_key_upload); only the shard's ranges go to the device. */
+int zkb_key_upload_shard(zkb_ctx *ctx, const zkb_key_desc *desc, int rank, int world, zkb_key **out);
+int zkb_prove_partial(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4],
+                      zkb_partial *out, uint64_t *H_out);
+int zkb_prove_combine(zkb_ctx *ctx, const zkb_partial *parts, size_t n, const uint64_t r[4], const uint64_t s[4],
+                      zkb_proof *out);
+
 /* `count` independent proofs under one key; w, r, s, out are arrays of `count` items
  * (w: count x num_variables x 4).  The batch is pipelined on the context's device. */
 int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r,

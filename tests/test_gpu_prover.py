@@ -160,6 +160,53 @@ def test_sha_chain_circuit(zctx, ref):
     circ.free()
 
 
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_one_proof_sharded_over_ranks(zctx, ref, world):
+    """one proof over `world` shards (one GPU plays every rank): every shard holds its range of the four
+    queries, computes its shares, zkb_prove_combine sums and assembles -> bytes identical to the reference proof.
+    A whole key refuses zkb_prove_partial-less use of a shard key."""
+    circ = ref.Circuit.example(1013, 10, seed=21)
+    circ.setup()
+    kd = circ.export_key()
+    w = circ.witness()
+    r = ref.sha512_rng(31, 1)[0]
+    s = ref.sha512_rng(32, 1)[0]
+    exp = circ.prove(w, r, s, want_H=False)
+    parts = []
+    for rank in range(world):
+        key = zctx.upload_key(kd, rank, world)
+        if rank == 1:
+            key.tune(w)  # tuning a shard must not change its share
+            with pytest.raises(zk.ZkbError):
+                zctx.prove(key, w, r, s)
+        parts.append(zctx.prove_partial(key, w, r, s))
+        key.free()
+    got = zctx.prove_combine(np.stack(parts), r, s)
+    assert ref.proof_bytes(got) == ref.proof_bytes(exp["proof"])
+    assert circ.verify(w[:10], got)
+    circ.free()
+
+
+def test_sharded_zklaim_proof_more_ranks_than_some_ranges(zctx, ref, zklaim1):
+    """the zklaim circuit over 4 shards through sharding.sharded_prove's building blocks; plus world = 1 == zkb_prove"""
+    from zklaim_b200 import sharding
+    circ, key1 = zklaim1
+    kd = circ.export_key()
+    w = circ.witness()
+    r = ref.sha512_rng(41, 1)[0]
+    s = ref.sha512_rng(42, 1)[0]
+    whole = zctx.prove(key1, w, r, s)
+    parts = []
+    for rank in range(4):
+        key = zctx.upload_key(kd, rank, 4)
+        parts.append(zctx.prove_partial(key, w, r, s))
+        key.free()
+    got = zctx.prove_combine(np.stack(parts), r, s)
+    assert ref.proof_bytes(got) == ref.proof_bytes(whole)
+    solo = sharding.sharded_prove(zctx, key1, w, r, s)  # no process group: a world of one
+    assert ref.proof_bytes(solo) == ref.proof_bytes(whole)
+
+
 def test_unsatisfied_witness_is_reported(zctx, ref, zklaim1):
     circ, key = zklaim1
     w = circ.witness().copy()

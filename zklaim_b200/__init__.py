@@ -55,6 +55,9 @@ SYMBOLS = {
     "zkb_key_free": (None, [_vp]),
     "zkb_key_device_bytes": (_sz, [_vp]),
     "zkb_key_domain": (_i, [_vp, C.POINTER(_sz), C.POINTER(_i)]),
+    "zkb_key_upload_shard": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
+    "zkb_prove_partial": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _u64p, _u64p]),
+    "zkb_prove_combine": (_i, [_vp, _u64p, _sz, _u64p, _u64p, _vp]),
     "zkb_key_tune": (_i, [_vp, _vp, _u64p]),
     "zkb_key_windows": (_i, [_vp, C.POINTER(_i)]),
     "zkb_witness_map": (_i, [_vp, _vp, _u64p, _u64p]),
@@ -234,8 +237,9 @@ class Context:
         return d
 
     # ---- key / prover -----------------------------------------------------------------
-    def upload_key(self, key: dict) -> "Key":
-        """key: dict with the fields of zkb_key_desc as numpy arrays (bridge: zkb_libsnark.hpp flattens a libsnark proving key into them)."""
+    def upload_key(self, key: dict, rank: int = 0, world: int = 1) -> "Key":
+        """key: dict with the fields of zkb_key_desc as numpy arrays (bridge: zkb_libsnark.hpp flattens a libsnark proving key
+        into them).  world > 1: only shard `rank`'s range of every query goes to the device (zkb_key_upload_shard)."""
         keep = []
 
         def ptr(a, dtype=np.uint64):
@@ -255,8 +259,22 @@ class Context:
         d.B_nnz = len(key["B_index"])
         d.H_size = len(key["H_query"])
         h = C.c_void_p()
-        self._chk(self.lib.zkb_key_upload(self.h, C.byref(d), C.byref(h)))
+        self._chk(self.lib.zkb_key_upload_shard(self.h, C.byref(d), rank, world, C.byref(h)))
         return Key(self, h, key["num_variables"])
+
+    def prove_partial(self, key: "Key", w, r, s) -> np.ndarray:
+        """this shard's share of the four sums of a proof: 60 uint64 = A (12), B1 (12), C (12), B2 (24) Jacobian limbs"""
+        w, r, s = _arr(w, 4), _arr(r, 4), _arr(s, 4)
+        out = np.zeros(60, dtype=np.uint64)
+        self._chk(self.lib.zkb_prove_partial(self.h, key.h, w.ctypes.data, r.ctypes.data, s.ctypes.data, out.ctypes.data, None))
+        return out
+
+    def prove_combine(self, parts, r, s) -> np.ndarray:
+        """adds up the shares of all shards and assembles the proof (r1cs_gg_ppzksnark.tcc:487-495)"""
+        parts, r, s = _arr(parts, 60), _arr(r, 4), _arr(s, 4)
+        pr = Proof()
+        self._chk(self.lib.zkb_prove_combine(self.h, parts.ctypes.data, parts.size // 60, r.ctypes.data, s.ctypes.data, C.byref(pr)))
+        return pr.as_array()
 
     def witness_map(self, key: "Key", w) -> np.ndarray:
         w = _arr(w, 4)

@@ -52,6 +52,7 @@ struct zkb_key {
     MsmPlan g1ab, g1c, g2;              // see the header: jobs {A, B1}, {C}, {B2}
     std::vector<uint32_t> h_sidx[3];    // host copies of the scalar maps (g1ab, g1c, g2), for zkb_key_tune
     size_t nnzB = 0;
+    int shard_rank = 0, shard_world = 1; // which contiguous range of every query this key holds
     size_t zlen = 0; // elements per row of Z
     size_t bytes = 0;
     // offsets into a row of Z
@@ -299,13 +300,13 @@ __device__ __forceinline__ void run(const uint32_t (*prog)[4], int nsteps, uint3
 } // namespace vm
 
 __global__ void __launch_bounds__(64)
-k_smul(const G1X *__restrict__ rab, const Fr *__restrict__ Pl, size_t zlen, size_t nv, G1X *__restrict__ sm)
+k_smul(const G1X *__restrict__ rab, const Fr *__restrict__ Pl, size_t zlen, size_t off_r, size_t off_s, G1X *__restrict__ sm)
 {
     __shared__ Fq regs[2][96];
     const int p = blockIdx.x, which = threadIdx.x >> 5, lane = threadIdx.x & 31; // 0: s * g1_A, 1: r * g1_B
     if (lane >= 4) return;
     Fq *Rg = regs[which];
-    const Fr k = ld_vec(Pl + (size_t)p * zlen + (which == 0 ? nv + 2 : nv + 1));
+    const Fr k = ld_vec(Pl + (size_t)p * zlen + (which == 0 ? off_s : off_r)); // plain integers
     const G1X *src = rab + 2 * (size_t)p + which;
     G1X *dst = sm + 2 * (size_t)p + which;
     const Fq *srcw = reinterpret_cast<const Fq *>(src);
@@ -371,6 +372,41 @@ k_assemble(const G1X *__restrict__ rab, const G1X *__restrict__ rc, const G1X *_
     st_vec(reinterpret_cast<G1J *>(out[p].A), ld_vec(rab + 2 * (size_t)p).to_jacobian());
     st_vec(reinterpret_cast<G1J *>(out[p].C), c.to_jacobian());
     st_vec(reinterpret_cast<G2J *>(out[p].B), ld_vec(r2 + p).to_jacobian());
+}
+
+// a shard's share of the four sums of one proof, as Jacobian limbs (zkb_prove_partial)
+__global__ void k_export_partial(const G1X *__restrict__ rab, const G1X *__restrict__ rc, const G2X *__restrict__ r2, int batch,
+                                 zkb_partial *__restrict__ out)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= batch) return;
+    st_vec(reinterpret_cast<G1J *>(out[p].A), ld_vec(rab + 2 * (size_t)p).to_jacobian());
+    st_vec(reinterpret_cast<G1J *>(out[p].B1), ld_vec(rab + 2 * (size_t)p + 1).to_jacobian());
+    st_vec(reinterpret_cast<G1J *>(out[p].C), ld_vec(rc + p).to_jacobian());
+    st_vec(reinterpret_cast<G2J *>(out[p].B2), ld_vec(r2 + p).to_jacobian());
+}
+
+// sums the shares of n shards (multiexp.tcc:433-438) into the layout k_smul / k_assemble expect; rs: r, s Montgomery -> plain
+__global__ void k_combine_partials(const zkb_partial *__restrict__ parts, int n, const Fr *__restrict__ rs, G1X *__restrict__ rab,
+                                   G1X *__restrict__ rc, G2X *__restrict__ r2, Fr *__restrict__ rs_plain)
+{
+    const int t = threadIdx.x >> 5; // one warp per component: divergent code stays in separate warps
+    if (threadIdx.x & 31) return;
+    if (t < 3) {
+        G1X acc = G1X::inf();
+        for (int i = 0; i < n; i++) {
+            const uint64_t *src = t == 0 ? parts[i].A : t == 1 ? parts[i].B1 : parts[i].C;
+            acc.add(G1X::from_jacobian(ld_vec(reinterpret_cast<const G1J *>(src))));
+        }
+        st_vec(t == 2 ? rc : rab + t, acc);
+    } else if (t == 3) {
+        G2X acc = G2X::inf();
+        for (int i = 0; i < n; i++) acc.add(G2X::from_jacobian(ld_vec(reinterpret_cast<const G2J *>(parts[i].B2))));
+        st_vec(r2, acc);
+    } else {
+        st_vec(rs_plain, ld_vec(rs).from_mont());
+        st_vec(rs_plain + 1, ld_vec(rs + 1).from_mont());
+    }
 }
 
 } // namespace
@@ -454,7 +490,7 @@ void key_release(zkb_key *key)
     delete key;
 }
 
-int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key)
+int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key, int rank, int world)
 {
     key->dev = ctx->dev;
     key->nc = d->num_constraints;
@@ -489,7 +525,85 @@ int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key)
     key->nnzB = d->B_nnz;
 
     // ---- MSM plans: {A, B1}, {C} in G1 and {B2} in G2 ----
-    const size_t nA = nv + 3, nB = d->B_nnz + 2, nL = nv - ni, nC = (m - 1) + nL + 1;
+    // A shard (rank of world) keeps the contiguous range [lo, hi) of every query -- libff's own chunking,
+    // multiexp.tcc:417-431 -- and rank 0 also keeps the fixed key elements; world == 1 is the whole key.
+    auto range = [&](size_t total, size_t &lo, size_t &hi) {
+        if (total < (size_t)world || world == 1) {
+            lo = 0;
+            hi = rank == 0 ? total : 0;
+            return;
+        }
+        const size_t one = total / world;
+        lo = rank * one;
+        hi = rank == world - 1 ? total : lo + one;
+    };
+    const size_t nL_all = nv - ni;
+    size_t loA, hiA, loB, hiB, loH, hiH, loL, hiL;
+    range(nv + 1, loA, hiA);
+    range(d->B_nnz, loB, hiB);
+    range(m - 1, loH, hiH);
+    range(nL_all, loL, hiL);
+    const bool fixed = rank == 0; // alpha, beta, delta ride along on rank 0 only
+    key->shard_rank = rank;
+    key->shard_world = world;
+    static const uint64_t inf_pt[16] = {0};
+    std::vector<uint64_t> stA, stB, stC, stB2;
+    std::vector<uint32_t> &sab = key->h_sidx[0], &sc = key->h_sidx[1], &s2 = key->h_sidx[2];
+    // job A
+    append_pts(stA, d->A_query + 8 * loA, hiA - loA, 8);
+    for (size_t i = loA; i < hiA; i++) sab.push_back((uint32_t)i);
+    if (fixed) {
+        append_pts(stA, d->alpha_g1, 1, 8);
+        append_pts(stA, d->delta_g1, 1, 8);
+        sab.push_back(0);
+        sab.push_back((uint32_t)key->z_r());
+    }
+    if (stA.empty()) { // an empty range still needs one (neutral) item: the point at infinity
+        append_pts(stA, inf_pt, 1, 8);
+        sab.push_back(0);
+    }
+    const size_t nA = stA.size() / 8;
+    // job B1 / B2
+    if (hiB > loB) {
+        append_pts(stB, d->B_g1 + 8 * loB, hiB - loB, 8);
+        append_pts(stB2, d->B_g2 + 16 * loB, hiB - loB, 16);
+    }
+    for (size_t k = loB; k < hiB; k++) {
+        sab.push_back(d->B_index[k]);
+        s2.push_back(d->B_index[k]);
+    }
+    if (fixed) {
+        append_pts(stB, d->beta_g1, 1, 8);
+        append_pts(stB, d->delta_g1, 1, 8);
+        append_pts(stB2, d->beta_g2, 1, 16);
+        append_pts(stB2, d->delta_g2, 1, 16);
+        for (std::vector<uint32_t> *v : {&sab, &s2}) {
+            v->push_back(0);
+            v->push_back((uint32_t)key->z_s());
+        }
+    }
+    if (stB.empty()) {
+        append_pts(stB, inf_pt, 1, 8);
+        append_pts(stB2, inf_pt, 1, 16);
+        sab.push_back(0);
+        s2.push_back(0);
+    }
+    const size_t nB = stB.size() / 8;
+    // job C
+    append_pts(stC, d->H_query + 8 * loH, hiH - loH, 8);
+    for (size_t j = loH; j < hiH; j++) sc.push_back((uint32_t)(key->z_h() + j));
+    if (hiL > loL) append_pts(stC, d->L_query + 8 * loL, hiL - loL, 8);
+    for (size_t j = loL; j < hiL; j++) sc.push_back((uint32_t)(1 + ni + j));
+    if (fixed) {
+        append_pts(stC, d->delta_g1, 1, 8);
+        sc.push_back((uint32_t)key->z_nrs());
+    }
+    if (stC.empty()) {
+        append_pts(stC, inf_pt, 1, 8);
+        sc.push_back(0);
+    }
+    const size_t nC = stC.size() / 8;
+
     key->g1ab.group = ZKB_G1;
     key->g1c.group = ZKB_G1;
     key->g2.group = ZKB_G2;
@@ -497,54 +611,15 @@ int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key)
     // mixed-addition variants for them); H is dense.  zkb_key_tune refines the guess from a real witness.
     if ((rc = plan_add_job(ctx, &key->g1ab, nA, msm_choose_c(nA / 4 + 1, ZKB_G1, 0), 0))) return rc;
     if ((rc = plan_add_job(ctx, &key->g1ab, nB, msm_choose_c(nB / 4 + 1, ZKB_G1, 0), 0))) return rc;
-    if ((rc = plan_add_job(ctx, &key->g1c, nC, msm_choose_c((m - 1) + nL / 4 + 1, ZKB_G1, 0), 0))) return rc;
+    if ((rc = plan_add_job(ctx, &key->g1c, nC, msm_choose_c((hiH - loH) + (hiL - loL) / 4 + 1, ZKB_G1, 0), 0))) return rc;
     if ((rc = plan_add_job(ctx, &key->g2, nB, msm_choose_c(nB / 4 + 1, ZKB_G2, 0), 0))) return rc;
     if ((rc = plan_alloc(ctx, &key->g1ab))) return rc;
     if ((rc = plan_alloc(ctx, &key->g1c))) return rc;
     if ((rc = plan_alloc(ctx, &key->g2))) return rc;
-
-    std::vector<uint64_t> st;
-    std::vector<uint32_t> &sab = key->h_sidx[0], &sc = key->h_sidx[1], &s2 = key->h_sidx[2];
-    sab.reserve(nA + nB);
-    st.reserve(nC * 8);
-    // job A
-    append_pts(st, d->A_query, nv + 1, 8);
-    append_pts(st, d->alpha_g1, 1, 8);
-    append_pts(st, d->delta_g1, 1, 8);
-    for (size_t i = 0; i <= nv; i++) sab.push_back((uint32_t)i);
-    sab.push_back(0);
-    sab.push_back((uint32_t)key->z_r());
-    if ((rc = plan_upload_job<Fq>(ctx, &key->g1ab, 0, st.data()))) return rc;
-    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    // job B1
-    st.clear();
-    append_pts(st, d->B_g1, d->B_nnz, 8);
-    append_pts(st, d->beta_g1, 1, 8);
-    append_pts(st, d->delta_g1, 1, 8);
-    for (size_t k = 0; k < d->B_nnz; k++) sab.push_back(d->B_index[k]);
-    sab.push_back(0);
-    sab.push_back((uint32_t)key->z_s());
-    if ((rc = plan_upload_job<Fq>(ctx, &key->g1ab, 1, st.data()))) return rc;
-    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    // job C
-    st.clear();
-    append_pts(st, d->H_query, m - 1, 8);
-    append_pts(st, d->L_query, nL, 8);
-    append_pts(st, d->delta_g1, 1, 8);
-    for (size_t j = 0; j + 1 < m; j++) sc.push_back((uint32_t)(key->z_h() + j));
-    for (size_t j = 0; j < nL; j++) sc.push_back((uint32_t)(1 + ni + j));
-    sc.push_back((uint32_t)key->z_nrs());
-    if ((rc = plan_upload_job<Fq>(ctx, &key->g1c, 0, st.data()))) return rc;
-    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    // job B2
-    st.clear();
-    append_pts(st, d->B_g2, d->B_nnz, 16);
-    append_pts(st, d->beta_g2, 1, 16);
-    append_pts(st, d->delta_g2, 1, 16);
-    for (size_t k = 0; k < d->B_nnz; k++) s2.push_back(d->B_index[k]);
-    s2.push_back(0);
-    s2.push_back((uint32_t)key->z_s());
-    if ((rc = plan_upload_job<Fq2>(ctx, &key->g2, 0, st.data()))) return rc;
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1ab, 0, stA.data()))) return rc;
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1ab, 1, stB.data()))) return rc;
+    if ((rc = plan_upload_job<Fq>(ctx, &key->g1c, 0, stC.data()))) return rc;
+    if ((rc = plan_upload_job<Fq2>(ctx, &key->g2, 0, stB2.data()))) return rc;
     ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 
     MsmPlan *plans[3] = {&key->g1ab, &key->g1c, &key->g2};
@@ -664,7 +739,7 @@ int stage_rows(zkb_ctx *ctx, const zkb_key *key, int batch, const Fr *d_rs, uint
 }
 
 // the witness-only MSM runs and the two scalar multiplications, on the side streams (forked after stage_rows)
-int msm_side_lanes(zkb_ctx *ctx, const zkb_key *key, int batch)
+int msm_side_lanes(zkb_ctx *ctx, const zkb_key *key, int batch, bool partial)
 {
     const uint32_t *P = ctx->scratch[SP_P].as<uint32_t>();
     ZKB_CUDA(ctx, ctx->scratch[SP_RES_AB].ensure((size_t)2 * batch * sizeof(G1X)));
@@ -678,8 +753,10 @@ int msm_side_lanes(zkb_ctx *ctx, const zkb_key *key, int batch)
         ZKB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_fork, 0));
         int rc = msm_run<Fq>(ctx, &key->g1ab, key->g1ab.tab, P, key->zlen * 8, batch, rab);
         if (rc) return rc;
-        k_smul<<<batch, 64, 0, ctx->stream>>>(rab, ctx->scratch[SP_P].as<Fr>(), key->zlen, key->nv, sm);
-        ZKB_LAUNCH_CHECK(ctx);
+        if (!partial) {
+            k_smul<<<batch, 64, 0, ctx->stream>>>(rab, ctx->scratch[SP_P].as<Fr>(), key->zlen, key->z_r(), key->z_s(), sm);
+            ZKB_LAUNCH_CHECK(ctx);
+        }
         ZKB_CUDA(ctx, cudaEventRecord(ctx->ev_join[0], ctx->stream));
     }
     {
@@ -693,7 +770,7 @@ int msm_side_lanes(zkb_ctx *ctx, const zkb_key *key, int batch)
 }
 
 // job C (needs H) on the main stream, then the join with the side lanes and the assembly
-int msm_main_lane_and_assemble(zkb_ctx *ctx, const zkb_key *key, int batch, zkb_proof *d_out)
+int msm_main_lane_and_assemble(zkb_ctx *ctx, const zkb_key *key, int batch, zkb_proof *d_out, zkb_partial *d_part)
 {
     const uint32_t *P = ctx->scratch[SP_P].as<uint32_t>();
     ZKB_CUDA(ctx, ctx->scratch[SP_RES_C].ensure((size_t)batch * sizeof(G1X)));
@@ -702,8 +779,12 @@ int msm_main_lane_and_assemble(zkb_ctx *ctx, const zkb_key *key, int batch, zkb_
     if (rc) return rc;
     ZKB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[0], 0));
     ZKB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[1], 0));
-    k_assemble<<<ceil_div((size_t)batch, 64), 64, 0, ctx->stream>>>(ctx->scratch[SP_RES_AB].as<G1X>(), rc_, ctx->scratch[SP_SMUL].as<G1X>(),
-                                                                  ctx->scratch[SP_RES2].as<G2X>(), batch, d_out);
+    if (d_part)
+        k_export_partial<<<ceil_div((size_t)batch, 64), 64, 0, ctx->stream>>>(ctx->scratch[SP_RES_AB].as<G1X>(), rc_,
+                                                                            ctx->scratch[SP_RES2].as<G2X>(), batch, d_part);
+    else
+        k_assemble<<<ceil_div((size_t)batch, 64), 64, 0, ctx->stream>>>(ctx->scratch[SP_RES_AB].as<G1X>(), rc_, ctx->scratch[SP_SMUL].as<G1X>(),
+                                                                      ctx->scratch[SP_RES2].as<G2X>(), batch, d_out);
     ZKB_LAUNCH_CHECK(ctx);
     return ZKB_OK;
 }
@@ -714,10 +795,14 @@ namespace {
 
 // shared body of zkb_witness_map / zkb_prove*: `dev_in` says whether w, r, s are device pointers
 int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r, const uint64_t *s,
-               bool dev_in, zkb_proof *out, uint64_t *H_out, bool map_only)
+               bool dev_in, zkb_proof *out, uint64_t *H_out, bool map_only, zkb_partial *part_out = nullptr)
 {
-    if (!ctx || !key || !w || (!map_only && (!r || !s || !out))) return fail(ctx, ZKB_ERR_ARG, "zkb_prove: bad argument");
+    if (!ctx || !key || !w || (!map_only && (!r || !s || (!out && !part_out)))) return fail(ctx, ZKB_ERR_ARG, "zkb_prove: bad argument");
     if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_prove: key lives on another device");
+    if (!map_only && !part_out && key->shard_world != 1)
+        return fail(ctx, ZKB_ERR_ARG, "zkb_prove: this key holds one shard of the queries: use zkb_prove_partial + zkb_prove_combine");
+    const bool partial = part_out != nullptr;
+    static_assert(sizeof(zkb_partial) >= sizeof(zkb_proof), "the proof staging buffer is sized for partials");
     if (count == 0) return ZKB_OK;
     ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
     cudaStream_t st = ctx->stream;
@@ -732,7 +817,7 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
         ZKB_CUDA(ctx, ctx->scratch[SP_P].ensure((size_t)batch * zlen * sizeof(Fr)));
         ZKB_CUDA(ctx, ctx->scratch[SP_RS].ensure((size_t)batch * 2 * sizeof(Fr)));
         ZKB_CUDA(ctx, ctx->scratch[SP_FLAGS].ensure((size_t)batch * 4));
-        ZKB_CUDA(ctx, ctx->scratch[SP_PROOF].ensure((size_t)batch * sizeof(zkb_proof)));
+        ZKB_CUDA(ctx, ctx->scratch[SP_PROOF].ensure((size_t)batch * sizeof(zkb_partial)));
         Fr *Z = ctx->scratch[SP_Z].as<Fr>();
         Fr *rs = ctx->scratch[SP_RS].as<Fr>();
         uint32_t *flags = ctx->scratch[SP_FLAGS].as<uint32_t>();
@@ -747,18 +832,19 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
         }
         ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
         int rc = stage_rows(ctx, key, batch, rs, flags);
-        if (!rc && !map_only) rc = msm_side_lanes(ctx, key, batch);
+        if (!rc && !map_only) rc = msm_side_lanes(ctx, key, batch, partial);
         if (!rc) rc = witness_map_chunk(ctx, key, batch, flags);
-        if (!rc && !map_only) rc = msm_main_lane_and_assemble(ctx, key, batch, d_out);
+        if (!rc && !map_only) rc = msm_main_lane_and_assemble(ctx, key, batch, d_out, partial ? (zkb_partial *)d_out : nullptr);
         if (rc) {
             cudaDeviceSynchronize(); // never leave a side stream running behind an error return
             return rc;
         }
         ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
-        const size_t pin_bytes = (size_t)batch * (sizeof(zkb_proof) + 4);
+        const size_t out_sz = partial ? sizeof(zkb_partial) : sizeof(zkb_proof);
+        const size_t pin_bytes = (size_t)batch * (out_sz + 4);
         if (ensure_pinned(ctx, pin_bytes)) return ZKB_ERR_CUDA;
-        uint32_t *h_flags = (uint32_t *)((char *)ctx->pinned + (size_t)batch * sizeof(zkb_proof));
-        if (!map_only) ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_out, (size_t)batch * sizeof(zkb_proof), cudaMemcpyDeviceToHost, st));
+        uint32_t *h_flags = (uint32_t *)((char *)ctx->pinned + (size_t)batch * out_sz);
+        if (!map_only) ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_out, (size_t)batch * out_sz, cudaMemcpyDeviceToHost, st));
         ZKB_CUDA(ctx, cudaMemcpyAsync(h_flags, flags, (size_t)batch * 4, cudaMemcpyDeviceToHost, st));
         if (H_out)
             ZKB_CUDA(ctx, cudaMemcpy2DAsync(H_out + base * (m + 1) * 4, (m + 1) * sizeof(Fr), Z + key->z_h(), zlen * sizeof(Fr),
@@ -768,7 +854,8 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
         cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
         total_ms += ms;
         prof_collect(ctx);
-        if (!map_only) memcpy(out + base, ctx->pinned, (size_t)batch * sizeof(zkb_proof));
+        if (!map_only && partial) memcpy(part_out + base, ctx->pinned, (size_t)batch * sizeof(zkb_partial));
+        if (!map_only && !partial) memcpy(out + base, ctx->pinned, (size_t)batch * sizeof(zkb_proof));
         for (int p = 0; p < batch; p++) unsat |= h_flags[p] != 0;
     }
     ctx->last_ms = total_ms;
@@ -780,16 +867,19 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
 
 extern "C" {
 
-int zkb_key_upload(zkb_ctx *ctx, const zkb_key_desc *desc, zkb_key **out)
+int zkb_key_upload(zkb_ctx *ctx, const zkb_key_desc *desc, zkb_key **out) { return zkb_key_upload_shard(ctx, desc, 0, 1, out); }
+
+int zkb_key_upload_shard(zkb_ctx *ctx, const zkb_key_desc *desc, int rank, int world, zkb_key **out)
 {
     if (!ctx || !desc || !out) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: bad argument");
+    if (world < 1 || rank < 0 || rank >= world) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload_shard: bad rank / world");
     if (!desc->alpha_g1 || !desc->beta_g1 || !desc->delta_g1 || !desc->beta_g2 || !desc->delta_g2 || !desc->A_query ||
         !desc->H_query || (desc->B_nnz && (!desc->B_index || !desc->B_g1 || !desc->B_g2)) ||
         (desc->num_variables > desc->num_inputs && !desc->L_query))
         return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: missing key arrays");
     ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
     zkb_key *key = new zkb_key();
-    const int rc = key_build(ctx, desc, key);
+    const int rc = key_build(ctx, desc, key, rank, world);
     if (rc) {
         key_release(key);
         return rc;
@@ -868,6 +958,46 @@ int zkb_prove(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_
               uint64_t *H_out)
 {
     return prove_impl(ctx, key, 1, w, r, s, false, out, H_out, false);
+}
+
+int zkb_prove_partial(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4],
+                      zkb_partial *out, uint64_t *H_out)
+{
+    if (!out) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_partial: out is NULL");
+    return prove_impl(ctx, key, 1, w, r, s, false, nullptr, H_out, false, out);
+}
+
+int zkb_prove_combine(zkb_ctx *ctx, const zkb_partial *parts, size_t n, const uint64_t r[4], const uint64_t s[4], zkb_proof *out)
+{
+    if (!ctx || !parts || !n || !r || !s || !out || n > 4096) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_combine: bad argument");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    cudaStream_t st = ctx->stream;
+    ZKB_CUDA(ctx, ctx->scratch[SP_W].ensure(n * sizeof(zkb_partial) + 4 * sizeof(Fr)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_RES_AB].ensure(2 * sizeof(G1X)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_RES_C].ensure(sizeof(G1X)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_RES2].ensure(sizeof(G2X)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_SMUL].ensure(2 * sizeof(G1X)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_PROOF].ensure(sizeof(zkb_partial)));
+    char *stage = ctx->scratch[SP_W].as<char>();
+    zkb_partial *d_parts = (zkb_partial *)stage;
+    Fr *d_rs = (Fr *)(stage + n * sizeof(zkb_partial)), *d_rs_plain = d_rs + 2;
+    ZKB_CUDA(ctx, cudaMemcpyAsync(d_parts, parts, n * sizeof(zkb_partial), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(d_rs, r, sizeof(Fr), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(d_rs + 1, s, sizeof(Fr), cudaMemcpyHostToDevice, st));
+    G1X *rab = ctx->scratch[SP_RES_AB].as<G1X>(), *rc = ctx->scratch[SP_RES_C].as<G1X>(), *sm = ctx->scratch[SP_SMUL].as<G1X>();
+    G2X *r2 = ctx->scratch[SP_RES2].as<G2X>();
+    zkb_proof *d_out = ctx->scratch[SP_PROOF].as<zkb_proof>();
+    k_combine_partials<<<1, 160, 0, st>>>(d_parts, (int)n, d_rs, rab, rc, r2, d_rs_plain);
+    ZKB_LAUNCH_CHECK(ctx);
+    k_smul<<<1, 64, 0, st>>>(rab, d_rs_plain, 0, 0, 1, sm);
+    ZKB_LAUNCH_CHECK(ctx);
+    k_assemble<<<1, 64, 0, st>>>(rab, rc, sm, r2, 1, d_out);
+    ZKB_LAUNCH_CHECK(ctx);
+    if (ensure_pinned(ctx, sizeof(zkb_proof))) return ZKB_ERR_CUDA;
+    ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_out, sizeof(zkb_proof), cudaMemcpyDeviceToHost, st));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(st));
+    memcpy(out, ctx->pinned, sizeof(zkb_proof));
+    return ZKB_OK;
 }
 
 int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r, const uint64_t *s,

@@ -68,3 +68,14 @@ def sharded_msm(ctx, group_id: int, bases_local, scalars_local: np.ndarray, grou
         part = ctx.group_sum(group_id, np.zeros((0, 12 if group_id == G1 else 24), dtype=np.uint64))
     parts = gather_partials(part, group, device)
     return (combine or ctx.group_sum)(group_id, parts)
+
+
+def sharded_prove(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndarray, group=None, device: Optional[str] = None) -> np.ndarray:
+    """ONE Groth16 proof over all ranks: `key_shard` = ctx.upload_key(key, rank, world) (this rank's range of the A, B, H
+    and L queries; rank 0 also alpha, beta, delta).  Every rank runs the witness map itself (replicas: a distributed NTT
+    would need an all-to-all of the whole vector per transform) and the MSMs over its ranges; the exchange is an
+    all_gather of one 480-byte share per rank; zkb_prove_combine adds the shares and does the assembly.  Returns the
+    proof (48 uint64: A, B, C Jacobian) on every rank."""
+    part = ctx.prove_partial(key_shard, w, r, s)
+    parts = gather_partials(part, group, device)
+    return ctx.prove_combine(parts, r, s)
