@@ -8,6 +8,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+if rank == 0:   # torchrun exports OMP_NUM_THREADS=1; the reference's setup / prover on rank 0 should use the host's cores
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
 torch.cuda.set_device(local)
 if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -44,6 +46,7 @@ for n in "ABC":
     kd["csr_" + n] = (z[f"csr_{n}_rp"], z[f"csr_{n}_col"], z[f"csr_{n}_co"])
 kd["num_constraints"], kd["num_variables"], kd["num_inputs"] = [int(x) for x in z["dims"]]
 w, r, s = z["w"], z["r"], z["s"]
+w = torch.from_numpy(w.view(np.int64)).pin_memory().numpy().view(np.uint64)   # pinned: the 124 MB witness copy runs at PCIe speed
 ctx = zk.Context(local)
 key = ctx.upload_key(kd, rank, world)
 key.tune(w)
