@@ -72,24 +72,45 @@ k_ntt_pass(Fr *__restrict__ data, size_t vstride, int L, int lobits, int k, int 
     for (int s = 0; s < k; s++) {
         const int b = DIT ? s : (k - 1 - s);
         const int sh = L - 1 - lobits - b;
-        for (int j = threadIdx.x; j < (E >> 1); j += NTT_T) {
-            const int col = j & (C - 1);
-            const int tt = j >> logC;
-            const int low = tt & ((1 << b) - 1);
-            const int t0 = ((tt >> b) << (b + 1)) | low;
-            const int i0 = (t0 << logC) + col, i1 = i0 + (1 << (b + logC));
-            const uint32_t lo = (col0 + col) & lomask;
-            const uint32_t ex = (((uint32_t)low << lobits) | lo) << sh;
-            const Fr w = ld_vec_ro(tw + ex);
-            const Fr u = smw_get(sm, E, i0);
-            Fr v = smw_get(sm, E, i1);
+        // two butterflies per iteration, loads first: two independent Montgomery products in flight per thread
+        for (int j = threadIdx.x; j < (E >> 1); j += 2 * NTT_T) {
+            int i0[2], i1[2];
+            Fr w[2], u[2], v[2];
+            const bool two = j + NTT_T < (E >> 1);
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+                const int jj = (q == 0 || two) ? j + q * NTT_T : j;
+                const int col = jj & (C - 1);
+                const int tt = jj >> logC;
+                const int low = tt & ((1 << b) - 1);
+                const int t0 = ((tt >> b) << (b + 1)) | low;
+                i0[q] = (t0 << logC) + col;
+                i1[q] = i0[q] + (1 << (b + logC));
+                const uint32_t lo = (col0 + col) & lomask;
+                const uint32_t ex = (((uint32_t)low << lobits) | lo) << sh;
+                w[q] = ld_vec_ro(tw + ex);
+                u[q] = smw_get(sm, E, i0[q]);
+                v[q] = smw_get(sm, E, i1[q]);
+            }
             if (DIT) {
-                v = v * w;
-                smw_put(sm, E, i0, u + v);
-                smw_put(sm, E, i1, u - v);
+#pragma unroll
+                for (int q = 0; q < 2; q++) v[q] = v[q] * w[q];
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    if (q == 1 && !two) break;
+                    smw_put(sm, E, i0[q], u[q] + v[q]);
+                    smw_put(sm, E, i1[q], u[q] - v[q]);
+                }
             } else {
-                smw_put(sm, E, i0, u + v);
-                smw_put(sm, E, i1, (u - v) * w);
+                Fr d[2];
+#pragma unroll
+                for (int q = 0; q < 2; q++) d[q] = (u[q] - v[q]) * w[q];
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    if (q == 1 && !two) break;
+                    smw_put(sm, E, i0[q], u[q] + v[q]);
+                    smw_put(sm, E, i1[q], d[q]);
+                }
             }
         }
         __syncthreads();
