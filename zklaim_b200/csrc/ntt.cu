@@ -29,6 +29,9 @@ namespace {
 constexpr int NTT_T = 256;     // threads per block
 constexpr int NTT_KMAX = 8;    // butterfly levels per pass
 constexpr int NTT_EMAX = 2048; // elements staged per block (64 KB of shared memory)
+#ifndef NTT_TFAST
+#define NTT_TFAST 1 // 1: lanes walk the t index in the staging loops (coalesced rows, but shared-memory stride C); 0: always the column index
+#endif
 
 __device__ __forceinline__ uint32_t brev(uint32_t x, int bits) { return bits ? (__brev(x) >> (32 - bits)) : 0u; }
 
@@ -58,7 +61,7 @@ k_ntt_pass(Fr *__restrict__ data, size_t vstride, int L, int lobits, int k, int 
     Fr *a = data + (size_t)blockIdx.y * vstride;
     const uint32_t col0 = blockIdx.x << logC;
     const uint32_t lomask = (1u << lobits) - 1u;
-    const bool tfast = lobits < logC;
+    const bool tfast = NTT_TFAST && lobits < logC;
 
     for (int e = threadIdx.x; e < E; e += NTT_T) {
         const int col = tfast ? (e >> k) : (e & (C - 1));
