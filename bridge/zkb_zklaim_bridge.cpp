@@ -22,6 +22,7 @@
 #include "zklaim/libsnark_wrapper.cpp" /* the reference bridge, unchanged */
 
 #include <chrono>
+#include <fcntl.h>
 #include <openssl/sha.h>
 
 #include "zkb_libsnark.hpp"
@@ -113,23 +114,31 @@ bool build_witness(zklaim_ctx *ctx, std::vector<FrT> &primary, std::vector<FrT> 
     return true;
 }
 
-struct StdoutMute { /* what libsnark_wrapper.cpp:221-226 / :245-246 do around every call */
+struct StdoutMute { /* what libsnark_wrapper.cpp:221-226 / :245-246 do around every call: the gadget prints to stdout */
     int saved;
     StdoutMute()
     {
         libff::inhibit_profiling_counters = 1;
         libff::inhibit_profiling_info = 1;
-        saved = dup(STDOUT_FILENO);
         fflush(stdout);
-        close(STDOUT_FILENO);
+        saved = dup(STDOUT_FILENO);
+        /* the reference close()s fd 1; pointing it at /dev/null silences the same output without leaving descriptor 1
+         * free for whoever opens a file next (CUDA, a profiler, another thread), who would then lose it on restore */
+        const int nul = open("/dev/null", O_WRONLY);
+        if (nul >= 0) {
+            dup2(nul, STDOUT_FILENO);
+            close(nul);
+        }
         std::cout.setstate(std::ios_base::failbit); /* the gadget streams every witness value to cout (:770, :781) */
     }
     ~StdoutMute()
     {
         fflush(stdout);
         std::cout.clear();
-        dup2(saved, STDOUT_FILENO);
-        close(saved);
+        if (saved >= 0) {
+            dup2(saved, STDOUT_FILENO);
+            close(saved);
+        }
     }
 };
 

@@ -60,6 +60,7 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *
     const bool medium = multi && !block_wide && (t1 - t0) >= FIXUP_WARP;
     const int n_medium = __popc(__ballot_sync(0xffffffffu, medium));
     const bool wide = medium && n_medium <= 4;
+    // (queueing the 16 .. 63-run spans of a crowded warp as well was measured: MSM 2^16 0.82 -> 2.4 ms; not done)
     if (block_wide) { // queue layout: [0] chunk count, [1] bucket count, chunks (b, index), bucket records (b, first chunk, chunks)
         const uint32_t n = (t1 - t0 + FIXUP_CHUNK) / FIXUP_CHUNK;
         const uint32_t first = atomicAdd(wide_list, n), rec = atomicAdd(wide_list + 1, 1u);
@@ -338,9 +339,9 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
             ZKB_CUDA(ctx, cudaFuncSetAttribute(k_fixup_wide<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FIXUP_WIDE_T * sizeof(PT))));
             ctx->func_attr_done |= attr_bit;
         }
-        k_fixup_wide<F><<<(unsigned)ctx->sm_count * 2, FIXUP_WIDE_T, FIXUP_WIDE_T * sizeof(PT), st>>>(start, (uint32_t)B, rmax, parts, wide, chunk_sums);
+        k_fixup_wide<F><<<(unsigned)ctx->sm_count * 16, FIXUP_WIDE_T, FIXUP_WIDE_T * sizeof(PT), st>>>(start, (uint32_t)B, rmax, parts, wide, chunk_sums);
         ZKB_LAUNCH_CHECK(ctx);
-        k_fixup_wide_sum<F><<<(unsigned)ctx->sm_count, 128, 128 * sizeof(PT), st>>>(buckets, wide, max_chunks, chunk_sums);
+        k_fixup_wide_sum<F><<<(unsigned)ctx->sm_count * 8, 128, 128 * sizeof(PT), st>>>(buckets, wide, max_chunks, chunk_sums);
         ZKB_LAUNCH_CHECK(ctx);
     }
     for (uint32_t q = 0; q < tab.njobs; q++) {
