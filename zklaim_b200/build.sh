@@ -6,7 +6,7 @@ OUT=../libzkb.so
 OBJ=../_obj
 mkdir -p $OBJ
 NVCC=${NVCC:-nvcc}
-FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -O2"
+FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -O2 $ZKB_EXTRA_NVCC_FLAGS"
 pids=()
 for src in *.cu; do
   o=$OBJ/${src%.cu}.o

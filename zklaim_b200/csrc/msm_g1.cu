@@ -1,5 +1,7 @@
 // msm_g1.cu -- G1 instantiation of the latency-bound MSM stages (noinline multiplier).
+#ifndef ZKB_INLINE_FINISH
 #define ZKB_NOINLINE_MUL 1
+#endif
 #include "msm_finish_impl.cuh"
 namespace zkb {
 template int msm_finish<Fq>(zkb_ctx *, const MsmPlan *, const JobTab &, int, uint32_t, XYZZ<Fq> *);
