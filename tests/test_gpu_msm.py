@@ -115,3 +115,37 @@ def test_range_sharded_msm_equals_whole(zctx, ref, group, n):
     zero = zctx.group_sum(group, np.zeros((0, w), dtype=np.uint64))
     _check(ref, group, zero, ref.group_op(group, 0, zero[None], zero[None])[0])  # 0 + 0 == 0: it is the identity
     _check(ref, group, zctx.group_sum(group, np.stack([exp, zero])), exp)
+
+
+def test_msm_properties_at_full_size(zctx, ref):
+    """BASELINE.json configs[2] size (2^22 points; multiexp_profile.cpp:45 runs 2^10 .. 2^20) through properties that
+    need no CPU run of that size: linearity MSM(a) + MSM(b) == MSM(a + b), the sum over contiguous ranges == the whole
+    (multiexp.tcc:417-438), and a prefix small enough for the reference == the reference.  Bases k_i * G come from
+    the GPU's own scalar multiplication (parity-tested against curve_utils.tcc:13-34 in test_gpu_ec.py)."""
+    n = 1 << 22
+    rng = np.random.default_rng(22)
+    one_q = ref.field_const(zk.FQ, 1)
+    g = np.concatenate([one_q, zctx.field_op(zk.FQ, zk.OP_ADD, one_q[None], one_q[None])[0], one_q])  # (1, 2, 1)
+
+    def rand_fr(m):
+        a = rng.integers(0, 1 << 64, size=(m, 4), dtype=np.uint64)
+        a[:, 3] &= np.uint64((1 << 60) - 1)
+        return a
+
+    bases = np.empty((n, 8), dtype=np.uint64)
+    step = 1 << 20
+    for lo in range(0, n, step):
+        P = zctx.scalar_mul(zk.G1, rand_fr(step), np.tile(g, (step, 1)))
+        bases[lo:lo + step] = zctx.group_op(zk.G1, zk.GOP_NORMALIZE, P)[:, :8]
+    a, b = rand_fr(n), rand_fr(n)
+    ab = zctx.field_op(zk.FR, zk.OP_ADD, a, b)
+    B = zctx.upload_bases(zk.G1, bases)
+    ra, rb, rab = zctx.msm(B, a), zctx.msm(B, b), zctx.msm(B, ab)
+    _check(ref, zk.G1, zctx.group_sum(zk.G1, np.stack([ra, rb])), rab)
+    cut = [0, n // 3, n // 2 + 12345, n]
+    parts = [zctx.msm(B, a[lo:hi], offset=lo) for lo, hi in zip(cut[:-1], cut[1:])]
+    _check(ref, zk.G1, zctx.group_sum(zk.G1, np.stack(parts)), ra)
+    k = 3000
+    exp, _ = ref.msm(zk.G1, bases[n - k:], a[n - k:])
+    _check(ref, zk.G1, zctx.msm(B, a[n - k:], offset=n - k), exp)
+    B.free()

@@ -239,3 +239,36 @@ def test_zklaim_five_payloads_step_domain(zctx, ref):
     _check_against_reference(zctx, ref, circ, key, circ.witness(), 31)
     key.free()
     circ.free()
+
+
+@pytest.mark.parametrize("nc,kind", [((1 << 18) - 11, zk.DOMAIN_BASIC_RADIX2), ((1 << 17) + (1 << 14) - 11, zk.DOMAIN_STEP_RADIX2)])
+def test_witness_map_at_scale_bit_exact(zctx, ref, nc, kind):
+    """BASELINE.json configs[3] (r1cs_to_qap_witness_map, r1cs_to_qap.tcc:205-334) on
+    generate_r1cs_example_with_field_input(m - 11, 10): all m + 1 H coefficients == the reference, at 2^18 and at a
+    step-radix-2 size.  The last constraint of these instances has ~m terms (the giant-row SpMV path).
+    The witness map needs the constraint system only, so the queries of the key are one generator each."""
+    mt = ref.available(mt=True)
+    circ = ref.Circuit.example(nc, 10, seed=nc, mt=mt)
+    d = circ.dims()
+    assert d["kind"] == kind
+    w = circ.witness()
+    g1 = ref.bases(zk.G1, 1, 1)[0]
+    g2 = ref.bases(zk.G2, 1, 1)[0]
+    nv, ni, m = d["num_variables"], d["num_inputs"], d["m"]
+    kd = dict(num_constraints=d["num_constraints"], num_variables=nv, num_inputs=ni,
+              csr_A=circ.csr(0), csr_B=circ.csr(1), csr_C=circ.csr(2),
+              alpha_g1=g1, beta_g1=g1, delta_g1=g1, beta_g2=g2, delta_g2=g2, A_query=np.tile(g1, (nv + 1, 1)),
+              B_index=np.zeros(1, dtype=np.uint32), B_g1=g1[None], B_g2=g2[None], H_query=np.tile(g1, (m - 1, 1)),
+              L_query=np.tile(g1, (nv - ni, 1)))
+    key = zctx.upload_key(kd)
+    H = zctx.witness_map(key, w)
+    Href, _ = circ.witness_map(w)
+    assert H.shape == Href.shape and np.array_equal(H, Href)
+    w2 = w.copy()
+    w2[ni + 5] = w[ni + 6]  # an unsatisfying assignment is reported, not mapped
+    if not np.array_equal(w2, w):
+        with pytest.raises(zk.ZkbError) as e:
+            zctx.witness_map(key, w2)
+        assert e.value.code == zk.ERR_UNSAT
+    key.free()
+    circ.free()
