@@ -209,6 +209,39 @@ int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64
 int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const void *d_w, const void *d_r,
                            const void *d_s, zkb_proof *out);
 
+/* ---- the generator ---------------------------------------------------------------
+ * r1cs_gg_ppzksnark_generator (r1cs_gg_ppzksnark.tcc:211-388) with its secret randomness supplied by the caller,
+ * the way zkb_prove takes (r, s): t, alpha, beta, gamma, delta (:221-225, Montgomery Fr) and the two random
+ * group generators (:284, :294; Jacobian limbs).  On the device: the Lagrange basis of the domain at t
+ * (basic_radix2_domain_aux.tcc:183-236, step_radix2_domain.tcc:161-186), A_i(t) / B_i(t) / C_i(t)
+ * (r1cs_to_qap.tcc:105-170), the L and gamma_ABC scalars (:254-275), the powers of t for H (:277-282), and every
+ * fixed-base exponentiation (batch_exp / kc_batch_exp / batch_exp_with_coeff, :303-333, :340-341) with 8-bit
+ * window tables.  The constraint system is passed as built; swap_AB_if_beneficial (r1cs.tcc:182-231, called at
+ * :217-218) is applied inside and reported in *swapped (the proving key holds the swapped system).
+ * Outputs are caller-allocated affine arrays (all-zero limbs = the zero of the group, which the reference's
+ * batch_to_special leaves as (0, 1, 0)); B is dense over num_variables + 1 entries, entries whose scalar is zero are
+ * the zero of the group (kc_batch_exp skips them, kc_multiexp.tcc:150-160: the sparse B_query = the non-zero ones).
+ * vk.alpha_g1_beta_g2 is one pairing of two outputs and stays with the caller (:338).
+ * Returns ZKB_ERR_ARG if t is an element of the domain (probability ~ m / 2^254; the reference special-cases it). */
+typedef struct {
+    size_t num_constraints, num_variables, num_inputs;
+    zkb_csr A, B, C;                                  /* as built, NOT swapped */
+    const uint64_t *t, *alpha, *beta, *gamma, *delta; /* 4 limbs each */
+    const uint64_t *g1_generator;                     /* 12 limbs */
+    const uint64_t *g2_generator;                     /* 24 limbs */
+} zkb_setup_desc;
+typedef struct {
+    uint64_t *alpha_g1, *beta_g1, *delta_g1; /* 8 limbs each */
+    uint64_t *beta_g2, *delta_g2, *gamma_g2; /* 16 limbs each */
+    uint64_t *A_query;                       /* (num_variables + 1) x 8 */
+    uint64_t *B_g1;                          /* (num_variables + 1) x 8 */
+    uint64_t *B_g2;                          /* (num_variables + 1) x 16 */
+    uint64_t *H_query;                       /* (m - 1) x 8, m = the domain size for num_constraints + num_inputs + 1 */
+    uint64_t *L_query;                       /* (num_variables - num_inputs) x 8 */
+    uint64_t *gamma_ABC_g1;                  /* (num_inputs + 1) x 8 */
+} zkb_setup_out;
+int zkb_setup(zkb_ctx *ctx, const zkb_setup_desc *desc, zkb_setup_out *out, int *swapped);
+
 /* ---- measurement helpers (used by bench.py only) ------------------------------------ */
 /* Sustained integer multiply-add rate of the device, measured with chains of dependent Fq Montgomery
  * products (136 multiply-adds of 32 x 32 + 64 -> 64 bits each, the instruction mix of every kernel here) on

@@ -774,6 +774,100 @@ double zkref_circuit_setup(void *h)
     return now_s() - t0;
 }
 
+/* The reference generator (r1cs_gg_ppzksnark.tcc:211-388) with its secret randomness injected: the reference draws
+ * t, alpha, beta, gamma, delta (:221-225) and the two group generators (:284, :294) from std::random_device and
+ * offers no way to fix them.  Same shape as prove_with_rs: the orchestration is re-expressed, every arithmetic call
+ * (swap_AB_if_beneficial, r1cs_to_qap_instance_map_with_evaluation, get_window_table, batch_exp, kc_batch_exp,
+ * batch_exp_with_coeff, batch_to_special, reduced_pairing) is the reference's own.
+ * toxic = t, alpha, beta, gamma, delta (5 x 4 limbs).  Returns seconds. */
+double zkref_circuit_setup_fixed(void *h, const u64 *toxic, const u64 *g1_gen, const u64 *g2_gen)
+{
+    Circuit *c = (Circuit *)h;
+    CoutSilencer quiet;
+    const double t0 = now_s();
+    r1cs_constraint_system<FrT> cs(c->cs);
+    cs.swap_AB_if_beneficial();
+    const FrT t = ld<FrT>(toxic), alpha = ld<FrT>(toxic + 4), beta = ld<FrT>(toxic + 8), gamma = ld<FrT>(toxic + 12),
+              delta = ld<FrT>(toxic + 16);
+    const G1T G = ld_g1(g1_gen);
+    const G2T Q = ld_g2(g2_gen);
+    qap_instance_evaluation<FrT> qap = r1cs_to_qap_instance_map_with_evaluation(cs, t);
+    const size_t nv = qap.num_variables(), ni = qap.num_inputs();
+    size_t nzA = 0, nzB = 0;
+    for (size_t i = 0; i <= nv; i++) {
+        nzA += qap.At[i].is_zero() ? 0 : 1;
+        nzB += qap.Bt[i].is_zero() ? 0 : 1;
+    }
+    const FrT ginv = gamma.inverse(), dinv = delta.inverse();
+    std::vector<FrT> abc(ni + 1), Lt(nv - ni), Ht(qap.Ht.begin(), qap.Ht.end() - 2);
+    for (size_t i = 0; i <= nv; i++) {
+        const FrT x = beta * qap.At[i] + alpha * qap.Bt[i] + qap.Ct[i];
+        if (i <= ni)
+            abc[i] = x * ginv;
+        else
+            Lt[i - ni - 1] = x * dinv;
+    }
+#ifdef MULTICORE
+    const size_t chunks = omp_get_max_threads();
+#else
+    const size_t chunks = 1;
+#endif
+    const size_t bits = FrT::size_in_bits();
+    const size_t w1 = libff::get_exp_window_size<G1T>(nzA + nzB + nv), w2 = libff::get_exp_window_size<G2T>(nzB);
+    const libff::window_table<G1T> T1 = libff::get_window_table(bits, w1, G);
+    const libff::window_table<G2T> T2 = libff::get_window_table(bits, w2, Q);
+    auto &pk = c->pk;
+    pk.alpha_g1 = alpha * G;
+    pk.beta_g1 = beta * G;
+    pk.beta_g2 = beta * Q;
+    pk.delta_g1 = delta * G;
+    pk.delta_g2 = delta * Q;
+    pk.A_query = libff::batch_exp(bits, w1, T1, qap.At);
+    libff::batch_to_special<G1T>(pk.A_query);
+    pk.B_query = kc_batch_exp(bits, w2, w1, T2, T1, FrT::one(), FrT::one(), qap.Bt, chunks);
+    for (auto &v : pk.B_query.values) { /* special form whatever USE_MIXED_ADDITION says */
+        v.g.to_special();
+        v.h.to_special();
+    }
+    pk.H_query = libff::batch_exp_with_coeff(bits, w1, T1, qap.Zt * dinv, Ht);
+    libff::batch_to_special<G1T>(pk.H_query);
+    pk.L_query = libff::batch_exp(bits, w1, T1, Lt);
+    libff::batch_to_special<G1T>(pk.L_query);
+    pk.constraint_system = cs;
+    std::vector<FrT> abc_rest(abc.begin() + 1, abc.end());
+    G1T abc0 = abc[0] * G;
+    std::vector<G1T> abc_vals = libff::batch_exp(bits, w1, T1, abc_rest);
+    c->vk = r1cs_gg_ppzksnark_verification_key<PP>(PP::reduced_pairing(pk.alpha_g1, pk.beta_g2), gamma * Q, pk.delta_g2,
+                                                   accumulation_vector<G1T>(std::move(abc0), std::move(abc_vals)));
+    c->has_key = true;
+    return now_s() - t0;
+}
+
+/* gamma_g2 (16), delta_g2 (16) and gamma_ABC_g1 ((num_inputs + 1) x 8) of the verification key, affine. */
+void zkref_vk_export(void *h, u64 *gamma_g2, u64 *delta_g2, u64 *gamma_abc)
+{
+    Circuit *c = (Circuit *)h;
+    st_g2_affine(gamma_g2, c->vk.gamma_g2);
+    st_g2_affine(delta_g2, c->vk.delta_g2);
+    st_g1_affine(gamma_abc, c->vk.gamma_ABC_g1.first);
+    for (size_t i = 0; i < c->vk.gamma_ABC_g1.rest.values.size(); i++)
+        st_g1_affine(gamma_abc + 8 * (i + 1), c->vk.gamma_ABC_g1.rest.values[i]);
+}
+
+/* Install a verification key made elsewhere (the GPU generator): alpha_g1 / beta_g2 for the one pairing of
+ * r1cs_gg_ppzksnark.tcc:338, gamma_g2, delta_g2, gamma_ABC_g1; zkref_verify then runs the reference verifier on it. */
+void zkref_vk_import(void *h, const u64 *alpha_g1, const u64 *beta_g2, const u64 *gamma_g2, const u64 *delta_g2,
+                     const u64 *gamma_abc, size_t n_abc)
+{
+    Circuit *c = (Circuit *)h;
+    std::vector<G1T> rest(n_abc - 1);
+    for (size_t i = 1; i < n_abc; i++) rest[i - 1] = ld_g1_affine(gamma_abc + 8 * i);
+    G1T first = ld_g1_affine(gamma_abc);
+    c->vk = r1cs_gg_ppzksnark_verification_key<PP>(PP::reduced_pairing(ld_g1_affine(alpha_g1), ld_g2_affine(beta_g2)),
+                                                   ld_g2_affine(gamma_g2), ld_g2_affine(delta_g2),
+                                                   accumulation_vector<G1T>(std::move(first), std::move(rest)));
+}
+
 /* sizes[0..5) = |A_query|, nnz(B_query), |H_query|, |L_query|, B_query domain size */
 void zkref_key_dims(void *h, size_t *sizes)
 {

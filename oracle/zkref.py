@@ -57,6 +57,9 @@ _SIG = {
     "zkref_key_dims": (None, [_vp, _vp]),
     "zkref_key_export": (None, [_vp] * 8),
     "zkref_key_import": (None, [_vp, _vp, _sz, _vp, _vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp]),
+    "zkref_circuit_setup_fixed": (_d, [_vp, _vp, _vp, _vp]),
+    "zkref_vk_export": (None, [_vp, _vp, _vp, _vp]),
+    "zkref_vk_import": (None, [_vp, _vp, _vp, _vp, _vp, _vp, _sz]),
     "zkref_witness_map": (_d, [_vp, _vp, _vp]),
     "zkref_prove": (_i, [_vp] * 8),
     "zkref_prove_stock": (_d, [_vp, _vp, _vp]),
@@ -255,6 +258,23 @@ class Circuit:
 
     def setup(self) -> float:
         return float(self.L.zkref_circuit_setup(self.h))
+
+    def setup_fixed(self, toxic, g1_gen, g2_gen) -> float:
+        """the reference generator with injected randomness: toxic = (t, alpha, beta, gamma, delta) as 5 x 4 limbs,
+        generators as Jacobian limbs (12 / 24)"""
+        t, g1, g2 = _u(toxic, 4), _u(g1_gen), _u(g2_gen)
+        assert t.shape == (5, 4) and g1.size == 12 and g2.size == 24
+        return float(self.L.zkref_circuit_setup_fixed(self.h, t.ctypes.data, g1.ctypes.data, g2.ctypes.data))
+
+    def export_vk(self) -> dict:
+        ni = self.dims()["num_inputs"]
+        g, d, abc = np.zeros(16, dtype=np.uint64), np.zeros(16, dtype=np.uint64), np.zeros((ni + 1, 8), dtype=np.uint64)
+        self.L.zkref_vk_export(self.h, g.ctypes.data, d.ctypes.data, abc.ctypes.data)
+        return {"gamma_g2": g, "delta_g2": d, "gamma_ABC_g1": abc}
+
+    def import_vk(self, alpha_g1, beta_g2, gamma_g2, delta_g2, gamma_abc):
+        a, b, g, d, abc = _u(alpha_g1), _u(beta_g2), _u(gamma_g2), _u(delta_g2), _u(gamma_abc, 8)
+        self.L.zkref_vk_import(self.h, a.ctypes.data, b.ctypes.data, g.ctypes.data, d.ctypes.data, abc.ctypes.data, len(abc))
 
     def export_key(self) -> dict:
         """the proving key as the flat arrays of zkb_key_desc"""

@@ -31,7 +31,7 @@ OP_ADD, OP_SUB, OP_MUL, OP_SQR, OP_INV, OP_NEG = range(6)
 GOP_ADD, GOP_DBL, GOP_MIXED_ADD, GOP_NEG, GOP_NORMALIZE = range(5)
 NTT_FFT, NTT_IFFT, NTT_COSET_FFT, NTT_ICOSET_FFT, NTT_DIV_Z_ON_COSET = range(5)
 DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2 = 1, 2, 3
-ERR_UNSAT = -4
+ERR_CUDA, ERR_ARG, ERR_DOMAIN, ERR_UNSAT = -1, -2, -3, -4
 
 # every symbol include/zkb.h declares: (name, restype, argtypes)
 _vp, _sz, _i, _u64p = C.c_void_p, C.c_size_t, C.c_int, C.c_void_p
@@ -60,6 +60,7 @@ SYMBOLS = {
     "zkb_prove_combine": (_i, [_vp, _u64p, _sz, _u64p, _u64p, _vp]),
     "zkb_key_tune": (_i, [_vp, _vp, _u64p]),
     "zkb_key_windows": (_i, [_vp, C.POINTER(_i)]),
+    "zkb_setup": (_i, [_vp, _vp, _vp, C.POINTER(_i)]),
     "zkb_witness_map": (_i, [_vp, _vp, _u64p, _u64p]),
     "zkb_prove": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _vp, _u64p]),
     "zkb_prove_batch": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p, _vp]),
@@ -121,6 +122,23 @@ class _KeyDesc(C.Structure):
         ("B_g1", C.c_void_p), ("B_g2", C.c_void_p),
         ("H_size", C.c_size_t), ("H_query", C.c_void_p), ("L_query", C.c_void_p),
     ]
+
+
+class _SetupDesc(C.Structure):
+    _fields_ = [
+        ("num_constraints", C.c_size_t), ("num_variables", C.c_size_t), ("num_inputs", C.c_size_t),
+        ("A", _CSR), ("B", _CSR), ("C", _CSR),
+        ("t", C.c_void_p), ("alpha", C.c_void_p), ("beta", C.c_void_p), ("gamma", C.c_void_p), ("delta", C.c_void_p),
+        ("g1_generator", C.c_void_p), ("g2_generator", C.c_void_p),
+    ]
+
+
+_SETUP_OUT = ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "delta_g2", "gamma_g2", "A_query", "B_g1", "B_g2", "H_query",
+              "L_query", "gamma_ABC_g1")
+
+
+class _SetupOut(C.Structure):
+    _fields_ = [(f, C.c_void_p) for f in _SETUP_OUT]
 
 
 class Proof(C.Structure):
@@ -261,6 +279,53 @@ class Context:
         h = C.c_void_p()
         self._chk(self.lib.zkb_key_upload_shard(self.h, C.byref(d), rank, world, C.byref(h)))
         return Key(self, h, key["num_variables"])
+
+    def setup(self, cs: dict, toxic, g1_gen, g2_gen) -> dict:
+        """zkb_setup: the Groth16 generator (r1cs_gg_ppzksnark.tcc:211-388) for the given secret randomness.
+        cs: num_constraints / num_variables / num_inputs + csr_A / csr_B / csr_C as built (not swapped);
+        toxic: (5, 4) limbs = t, alpha, beta, gamma, delta; generators as Jacobian limbs.
+        Returns the fields of zkb_key_desc (constraint system swapped when `swapped`, B_query sparse like the
+        reference's) plus gamma_g2, gamma_ABC_g1 of the verification key and `swapped`."""
+        keep = []
+
+        def ptr(a, dtype=np.uint64):
+            a = np.ascontiguousarray(a, dtype=dtype)
+            keep.append(a)
+            return a.ctypes.data
+
+        d = _SetupDesc()
+        nc, nv, ni = cs["num_constraints"], cs["num_variables"], cs["num_inputs"]
+        d.num_constraints, d.num_variables, d.num_inputs = nc, nv, ni
+        for name in "ABC":
+            rp, col, co = cs["csr_" + name]
+            setattr(d, name, _CSR(ptr(rp), ptr(col, np.uint32), ptr(co)))
+        toxic = _arr(toxic, 4)
+        if toxic.shape != (5, 4):
+            raise ValueError("toxic: expected 5 x 4 limbs")
+        for i, f in enumerate(("t", "alpha", "beta", "gamma", "delta")):
+            setattr(d, f, ptr(toxic[i]))
+        d.g1_generator, d.g2_generator = ptr(_arr(g1_gen, 12)), ptr(_arr(g2_gen, 24))
+        m = C.c_size_t()
+        kind = C.c_int()
+        self._chk(self.lib.zkb_domain_select(nc + ni + 1, C.byref(m), C.byref(kind)))
+        shapes = {"alpha_g1": (8,), "beta_g1": (8,), "delta_g1": (8,), "beta_g2": (16,), "delta_g2": (16,), "gamma_g2": (16,),
+                  "A_query": (nv + 1, 8), "B_g1": (nv + 1, 8), "B_g2": (nv + 1, 16), "H_query": (m.value - 1, 8),
+                  "L_query": (nv - ni, 8), "gamma_ABC_g1": (ni + 1, 8)}
+        res = {f: np.zeros(shapes[f], dtype=np.uint64) for f in _SETUP_OUT}
+        o = _SetupOut()
+        for f in _SETUP_OUT:
+            a = res[f] if res[f].size else np.zeros(8, dtype=np.uint64)
+            keep.append(a)
+            setattr(o, f, a.ctypes.data)
+        swapped = C.c_int()
+        self._chk(self.lib.zkb_setup(self.h, C.byref(d), C.byref(o), C.byref(swapped)))
+        nz = np.flatnonzero(res["B_g1"].any(axis=1))  # kc_batch_exp keeps the non-zero entries (kc_multiexp.tcc:108-116)
+        res["B_index"] = nz.astype(np.uint32)
+        res["B_g1"], res["B_g2"] = res["B_g1"][nz], res["B_g2"][nz]
+        a, b = ("B", "A") if swapped.value else ("A", "B")
+        res.update(num_constraints=nc, num_variables=nv, num_inputs=ni, csr_A=cs["csr_" + a], csr_B=cs["csr_" + b],
+                   csr_C=cs["csr_C"], swapped=bool(swapped.value))
+        return res
 
     def prove_partial(self, key: "Key", w, r, s) -> np.ndarray:
         """this shard's share of the four sums of a proof: 60 uint64 = A (12), B1 (12), C (12), B2 (24) Jacobian limbs"""

@@ -375,6 +375,11 @@ int scale(zkb_ctx *ctx, Fr *a, size_t vstride, size_t n, int nvec, const Fr *tab
 
 namespace zkb {
 
+Fr host_fr_from_u64(uint64_t x) { return fr_from_u64(x); }
+Fr host_fr_pow(Fr b, uint64_t e) { return fr_pow(b, e); }
+Fr host_fr_root_of_unity(int logn) { return fr_root_of_unity(logn); }
+int host_ceil_log2(size_t n) { return ceil_log2(n); }
+
 int domain_select_host(size_t min_size, size_t *m_out, int *kind_out)
 {
     if (min_size <= 1) return ZKB_ERR_DOMAIN;

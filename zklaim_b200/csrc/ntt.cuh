@@ -31,6 +31,11 @@ struct Domain {
 };
 
 int domain_select_host(size_t min_size, size_t *m_out, int *kind_out);
+// host-side constants of a domain (a handful of field operations per call, portable path of fp.cuh)
+Fr host_fr_from_u64(uint64_t x);
+Fr host_fr_pow(Fr b, uint64_t e);
+Fr host_fr_root_of_unity(int logn); // libff::get_root_of_unity<Fr>(2^logn), field_utils.tcc:44-60
+int host_ceil_log2(size_t n);       // libff::log2
 int domain_build(zkb_ctx *ctx, size_t m, int kind, Domain *d);
 void domain_free(Domain *d);
 

@@ -629,6 +629,9 @@ int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key, int rank, int w
         ZKB_CUDA(ctx, cudaMemcpy(plans[k]->d_sidx, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
         key->bytes += plans[k]->bytes + v.size() * 4;
     }
+    // the synchronous copies above come from pageable memory and may return before their DMA has landed; the
+    // context's streams are non-blocking, so make the key complete before anyone can enqueue work that reads it
+    ZKB_CUDA(ctx, cudaDeviceSynchronize());
     return ZKB_OK;
 }
 
