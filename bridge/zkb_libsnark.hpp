@@ -300,5 +300,130 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> prover(const libsnark::r1cs_gg_ppzksnark_
     return prover_with_rs(key, primary_input, auxiliary_input, r, s);
 }
 
+/* ---- the generator (include/zkb.h zkb_setup) ---------------------------------- */
+inline G1T get_g1_affine(const uint64_t *src)
+{
+    bool zero = true;
+    for (int i = 0; i < 8; i++) zero = zero && src[i] == 0;
+    return zero ? G1T::zero() : G1T(get_fp(src), get_fp(src + 4), libff::alt_bn128_Fq::one());
+}
+inline G2T get_g2_affine(const uint64_t *src)
+{
+    bool zero = true;
+    for (int i = 0; i < 16; i++) zero = zero && src[i] == 0;
+    return zero ? G2T::zero()
+                : G2T(libff::alt_bn128_Fq2(get_fp(src), get_fp(src + 4)), libff::alt_bn128_Fq2(get_fp(src + 8), get_fp(src + 12)),
+                      libff::alt_bn128_Fq2::one());
+}
+inline void put_g1_jacobian(uint64_t *dst, const G1T &p)
+{
+    put_fp(dst, p.X);
+    put_fp(dst + 4, p.Y);
+    put_fp(dst + 8, p.Z);
+}
+inline void put_g2_jacobian(uint64_t *dst, const G2T &p)
+{
+    put_fp(dst, p.X.c0);
+    put_fp(dst + 4, p.X.c1);
+    put_fp(dst + 8, p.Y.c0);
+    put_fp(dst + 12, p.Y.c1);
+    put_fp(dst + 16, p.Z.c0);
+    put_fp(dst + 20, p.Z.c1);
+}
+
+/* r1cs_gg_ppzksnark_generator (r1cs_gg_ppzksnark.tcc:211-388) with its randomness given (tests fix it; the drop-in
+ * below draws it): every field / group computation runs in zkb_setup, the objects are libsnark's. */
+inline libsnark::r1cs_gg_ppzksnark_keypair<PP> generator_with_randomness(const libsnark::r1cs_constraint_system<FrT> &r1cs, const FrT &t,
+                                                                         const FrT &alpha, const FrT &beta, const FrT &gamma,
+                                                                         const FrT &delta, const G1T &g1_gen, const G2T &g2_gen)
+{
+    KeyArrays k;
+    for (int w = 0; w < 3; w++) pack_matrix(r1cs, w, k);
+    const size_t nc = r1cs.num_constraints(), nv = r1cs.num_variables(), ni = r1cs.num_inputs();
+    size_t m = 0;
+    int kind = 0;
+    if (zkb_domain_select(nc + ni + 1, &m, &kind) != ZKB_OK) throw std::runtime_error("zkb_setup: no evaluation domain for this size");
+    uint64_t g1j[12], g2j[24];
+    put_g1_jacobian(g1j, g1_gen);
+    put_g2_jacobian(g2j, g2_gen);
+    zkb_setup_desc d;
+    memset(&d, 0, sizeof(d));
+    d.num_constraints = nc;
+    d.num_variables = nv;
+    d.num_inputs = ni;
+    zkb_csr *mats[3] = {&d.A, &d.B, &d.C};
+    for (int w = 0; w < 3; w++) {
+        mats[w]->row_ptr = k.row_ptr[w].data();
+        mats[w]->col = k.col[w].data();
+        mats[w]->coeff = k.coeff[w].data();
+    }
+    d.t = (const uint64_t *)t.mont_repr.data;
+    d.alpha = (const uint64_t *)alpha.mont_repr.data;
+    d.beta = (const uint64_t *)beta.mont_repr.data;
+    d.gamma = (const uint64_t *)gamma.mont_repr.data;
+    d.delta = (const uint64_t *)delta.mont_repr.data;
+    d.g1_generator = g1j;
+    d.g2_generator = g2j;
+    std::vector<uint64_t> sing(3 * 8 + 3 * 16), A((nv + 1) * 8), B1((nv + 1) * 8), B2((nv + 1) * 16), H(m * 8), L((nv - ni) * 8 + 8),
+        abc((ni + 1) * 8);
+    zkb_setup_out o;
+    o.alpha_g1 = &sing[0];
+    o.beta_g1 = &sing[8];
+    o.delta_g1 = &sing[16];
+    o.beta_g2 = &sing[24];
+    o.delta_g2 = &sing[40];
+    o.gamma_g2 = &sing[56];
+    o.A_query = A.data();
+    o.B_g1 = B1.data();
+    o.B_g2 = B2.data();
+    o.H_query = H.data();
+    o.L_query = L.data();
+    o.gamma_ABC_g1 = abc.data();
+    int swapped = 0;
+    zkb_ctx *ctx = Session::get().ctx();
+    if (zkb_setup(ctx, &d, &o, &swapped) != ZKB_OK) throw std::runtime_error(std::string("zkb_setup failed: ") + zkb_last_error(ctx));
+
+    libsnark::r1cs_constraint_system<FrT> cs(r1cs);
+    if (swapped)
+        for (auto &c : cs.constraints) std::swap(c.a, c.b); /* what swap_AB_if_beneficial did (r1cs.tcc:216-224) */
+    libff::G1_vector<PP> Aq(nv + 1), Hq(m - 1), Lq(nv - ni), abc_rest(ni);
+    for (size_t i = 0; i <= nv; i++) Aq[i] = get_g1_affine(&A[8 * i]);
+    for (size_t i = 0; i + 1 < m; i++) Hq[i] = get_g1_affine(&H[8 * i]);
+    for (size_t i = 0; i < nv - ni; i++) Lq[i] = get_g1_affine(&L[8 * i]);
+    for (size_t i = 0; i < ni; i++) abc_rest[i] = get_g1_affine(&abc[8 * (i + 1)]);
+    libsnark::knowledge_commitment_vector<G2T, G1T> Bq;
+    Bq.domain_size_ = nv + 1;
+    for (size_t i = 0; i <= nv; i++) {
+        const G1T h = get_g1_affine(&B1[8 * i]);
+        if (h.is_zero()) continue; /* kc_batch_exp keeps the non-zero scalars only (kc_multiexp.tcc:108-116) */
+        Bq.indices.push_back(i);
+        Bq.values.emplace_back(libsnark::knowledge_commitment<G2T, G1T>(get_g2_affine(&B2[16 * i]), h));
+    }
+    G1T alpha_g1 = get_g1_affine(o.alpha_g1), beta_g1 = get_g1_affine(o.beta_g1), delta_g1 = get_g1_affine(o.delta_g1);
+    G2T beta_g2 = get_g2_affine(o.beta_g2), delta_g2 = get_g2_affine(o.delta_g2), gamma_g2 = get_g2_affine(o.gamma_g2);
+    G1T abc0 = get_g1_affine(&abc[0]);
+    libsnark::accumulation_vector<G1T> gamma_ABC_g1(std::move(abc0), std::move(abc_rest));
+    /* the one pairing of the verification key stays libff's (r1cs_gg_ppzksnark.tcc:338) */
+    libsnark::r1cs_gg_ppzksnark_verification_key<PP> vk(PP::reduced_pairing(alpha_g1, beta_g2), gamma_g2, delta_g2, gamma_ABC_g1);
+    G2T delta_g2_pk = delta_g2;
+    libsnark::r1cs_gg_ppzksnark_proving_key<PP> pk(std::move(alpha_g1), std::move(beta_g1), std::move(beta_g2), std::move(delta_g1),
+                                                   std::move(delta_g2_pk), std::move(Aq), std::move(Bq), std::move(Hq), std::move(Lq),
+                                                   std::move(cs));
+    return libsnark::r1cs_gg_ppzksnark_keypair<PP>(std::move(pk), std::move(vk));
+}
+
+/* Drop-in for r1cs_gg_ppzksnark_generator<alt_bn128_pp> (r1cs_gg_ppzksnark.tcc:211-388): the randomness is drawn with
+ * the reference's own random_element() calls, in the reference's order (:221-225, :284, :294). */
+template <typename ppT>
+libsnark::r1cs_gg_ppzksnark_keypair<ppT> generator(const libsnark::r1cs_gg_ppzksnark_constraint_system<ppT> &r1cs)
+{
+    static_assert(std::is_same<ppT, PP>::value, "the zkb backend implements alt_bn128 only");
+    const FrT t = FrT::random_element(), alpha = FrT::random_element(), beta = FrT::random_element(), gamma = FrT::random_element(),
+              delta = FrT::random_element();
+    const G1T g1 = G1T::random_element();
+    const G2T g2 = G2T::random_element();
+    return generator_with_randomness(r1cs, t, alpha, beta, gamma, delta, g1, g2);
+}
+
 } // namespace zkb_bridge
 #endif /* ZKB_LIBSNARK_HPP */

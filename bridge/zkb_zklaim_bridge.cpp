@@ -146,6 +146,28 @@ struct StdoutMute { /* what libsnark_wrapper.cpp:221-226 / :245-246 do around ev
 
 extern "C" {
 
+/* Replacement of libsnark_trusted_setup (zklaim/zklaim.h:258, libsnark_wrapper.cpp:195-215): the constraint system
+ * comes from the reference's gadget exactly as in generate_keypair (snark.cpp:77-92), the generator runs on the GPU
+ * (zkb_bridge::generator -> zkb_setup), and both keys are serialised by the reference's own exporters. */
+int zkb_libsnark_trusted_setup(zklaim_ctx *ctx)
+{
+    StdoutMute mute;
+    ppT::init_public_params();
+    try {
+        protoboard<FrT> pb;
+        zklaim_gadget<FrT> g(pb, ctx);
+        g.generate_r1cs_constraints();
+        const r1cs_constraint_system<FrT> cs = pb.get_constraint_system();
+        r1cs_gg_ppzksnark_keypair<ppT> keypair = zkb_bridge::generator<ppT>(cs);
+        ctx->vk_size = libsnark_export_vk(keypair.vk, &ctx->vk);
+        ctx->pk_size = libsnark_export_pk(keypair.pk, &ctx->pk);
+        return 0;
+    } catch (const std::exception &e) {
+        fprintf(stderr, "zkb_libsnark_trusted_setup: %s\n", e.what());
+        return -1;
+    }
+}
+
 /* Replacement of libsnark_prove (zklaim/zklaim.h:259, libsnark_wrapper.cpp:218-250). */
 int zkb_libsnark_prove(zklaim_ctx *ctx)
 {
@@ -419,6 +441,25 @@ int zkbr_roundtrip(void *h, size_t count, uint64_t seed0, double *seconds)
     for (size_t i = 0; i < count; i++) ok += libsnark_verify(ptrs[i]) == 0 ? 1 : 0;
     seconds[1] = now_s() - t;
     return ok;
+}
+
+/* A `payloads`-payload credential end to end on a GPU-made key: zkb_libsnark_trusted_setup, then a proof by the
+ * reference's own CPU prover (stock = 1: libsnark_prove, unmodified) or by zkb_libsnark_prove (stock = 0), then the
+ * reference's libsnark_verify.  Returns libsnark_verify's result (0 = accepted), < 0 on an earlier failure;
+ * seconds[0] = setup, [1] = prove, [2] = verify. */
+int zkbr_setup_roundtrip(size_t payloads, uint64_t seed, int stock, double *seconds)
+{
+    Credential c(payloads, seed);
+    double t = now_s();
+    if (zkb_libsnark_trusted_setup(&c.ctx) != 0) return -1;
+    seconds[0] = now_s() - t;
+    t = now_s();
+    if ((stock ? libsnark_prove(&c.ctx) : zkb_libsnark_prove(&c.ctx)) != 0) return -2;
+    seconds[1] = now_s() - t;
+    t = now_s();
+    const int rc = libsnark_verify(&c.ctx);
+    seconds[2] = now_s() - t;
+    return rc;
 }
 
 } // extern "C"

@@ -48,3 +48,13 @@ def test_unsatisfied_credential_returns_one(cred):
         del os.environ["ZKB_HOST_CHECK"]
     ok, _, _ = cred.roundtrip(2, 4200)  # the session is still healthy afterwards
     assert ok == 2
+
+
+@pytest.mark.parametrize("stock_prover", [False, True])
+def test_trusted_setup_on_the_gpu_gives_a_key_the_reference_accepts(cred, stock_prover):
+    """SURVEY 8f row 2 through the zklaim entry points: zkb_libsnark_trusted_setup (zkb_setup on the GPU, keys
+    serialised by the reference's exporters) -> a proof by the reference's UNMODIFIED CPU libsnark_prove (or by
+    zkb_libsnark_prove) under that key -> the reference's libsnark_verify accepts (0)."""
+    from zklaim_b200 import bridge
+    rc, t_setup, t_prove, t_verify = bridge.setup_roundtrip(1, seed=11, stock_prover=stock_prover)
+    assert rc == 0

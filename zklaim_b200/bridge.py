@@ -30,6 +30,7 @@ _SIG = {
     "zkbr_verify": (_i, [_vp, _vp, _vp]),
     "zkbr_roundtrip": (_i, [_vp, _sz, _u64, _vp]),
     "zkbr_prove_tampered": (_i, [_vp, _u64]),
+    "zkbr_setup_roundtrip": (_i, [_sz, _u64, _i, _vp]),
 }
 _lib = None
 
@@ -102,3 +103,13 @@ class Credentials:
         if self.h:
             self.L.zkbr_free(self.h)
             self.h = None
+
+
+def setup_roundtrip(payloads: int = 1, seed: int = 1, stock_prover: bool = False):
+    """zkb_libsnark_trusted_setup (generator on the GPU) -> a proof under that key (the reference's unmodified CPU
+    libsnark_prove when stock_prover, else zkb_libsnark_prove) -> the reference's libsnark_verify.
+    Returns (libsnark_verify's result: 0 = accepted, setup s, prove s, verify s)."""
+    import ctypes as C
+    t = (C.c_double * 3)()
+    rc = int(lib().zkbr_setup_roundtrip(payloads, seed, 1 if stock_prover else 0, t))
+    return rc, t[0], t[1], t[2]
