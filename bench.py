@@ -311,6 +311,22 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def host_threads(impl):
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to every rank when the variable is unset.  The reference arm
+    must use all host threads it can (only rank 0 works there); our arm's host-side witness generation (outside
+    the timed region) shares the cores between the ranks.  Must run before anything loads an OpenMP runtime.
+    ZKB_HOST_THREADS overrides."""
+    if "TORCHELASTIC_RUN_ID" not in os.environ and "ZKB_HOST_THREADS" not in os.environ:
+        return
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    threads = n if impl == "reference" else max(1, n // world)
+    os.environ["OMP_NUM_THREADS"] = os.environ.get("ZKB_HOST_THREADS", str(threads))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -322,6 +338,7 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
+    host_threads(args.impl)
     if args.impl == "reference":
         run_reference(args)
     else:
