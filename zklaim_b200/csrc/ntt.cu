@@ -8,7 +8,7 @@
 // DFT gives bit-identical vectors; the schedule here is chosen for the GPU:
 //
 //   * a transform of size 2^L is cut into passes of at most 8 butterfly levels; a thread block
-//     stages C columns x 2^k elements in shared memory (word-planar, conflict-free), runs the
+//     stages C columns x 2^k elements in shared memory (word-planar, XOR-swizzled), runs the
 //     k levels there and writes back in place, so one pass costs one HBM read and one write
 //     of the vector, in 256-byte rows;
 //   * the witness map needs iFFT followed by cosetFFT: the inverse runs decimation-in-
@@ -35,16 +35,26 @@ constexpr int NTT_EMAX = 2048; // elements staged per block (64 KB of shared mem
 
 __device__ __forceinline__ uint32_t brev(uint32_t x, int bits) { return bits ? (__brev(x) >> (32 - bits)) : 0u; }
 
+// Word-planar staging with an XOR swizzle of the low five index bits by the next five: the transposing load / store
+// phase (lanes walk t, index stride C = 2 .. 8 words) would otherwise hit 32 / C banks only (ncu: 16.4 M conflicts
+// in 20 M shared-memory wavefronts of a 2^20 pass, profiles/r01_k_ntt_pass_ncu.txt); butterfly levels whose warp
+// touches 32 consecutive aligned indices stay conflict-free (the swizzle is a permutation inside such a group).
+#ifndef NTT_SWIZZLE
+#define NTT_SWIZZLE 1
+#endif
+__device__ __forceinline__ int smw_pos(int idx) { return NTT_SWIZZLE ? (idx ^ ((idx >> 5) & 31)) : idx; }
 __device__ __forceinline__ void smw_put(uint32_t *sm, int E, int idx, const Fr &v)
 {
+    const int p = smw_pos(idx);
 #pragma unroll
-    for (int i = 0; i < 8; i++) sm[i * E + idx] = v.v[i];
+    for (int i = 0; i < 8; i++) sm[i * E + p] = v.v[i];
 }
 __device__ __forceinline__ Fr smw_get(const uint32_t *sm, int E, int idx)
 {
+    const int p = smw_pos(idx);
     Fr v;
 #pragma unroll
-    for (int i = 0; i < 8; i++) v.v[i] = sm[i * E + idx];
+    for (int i = 0; i < 8; i++) v.v[i] = sm[i * E + p];
     return v;
 }
 
@@ -75,6 +85,9 @@ k_ntt_pass(Fr *__restrict__ data, size_t vstride, int L, int lobits, int k, int 
     for (int s = 0; s < k; s++) {
         const int b = DIT ? s : (k - 1 - s);
         const int sh = L - 1 - lobits - b;
+        // (measured and rejected: skipping the unit twiddles of the level on index bit 0 -- uniform per block and level,
+        //  bit-exact -- made the kernel slower, 8.4 -> 10.9 ms per witness map at 2^22: the conditional defeats the
+        //  two-butterfly software pipelining)
         // two butterflies per iteration, loads first: two independent Montgomery products in flight per thread
         for (int j = threadIdx.x; j < (E >> 1); j += 2 * NTT_T) {
             int i0[2], i1[2];
