@@ -209,6 +209,16 @@ int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64
 int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const void *d_w, const void *d_r,
                            const void *d_s, zkb_proof *out);
 
+/* Pipelined form of zkb_prove_batch for a stream of batches (a proving service): _submit starts the host-to-device
+ * copy of a batch's inputs on a copy stream and returns; _collect waits for the OLDEST submitted batch's inputs,
+ * proves it and returns its proofs.  Two staging slots alternate, so at most two batches may be submitted and not
+ * yet collected; with submit(k + 1) issued before collect(k) the input transfer of batch k + 1 overlaps the
+ * computation of batch k.  w, r, s must stay valid (and should be pinned) until the matching _collect returns.
+ * Results are those of zkb_prove_batch; ZKB_ERR_UNSAT is reported by the _collect of the offending batch. */
+int zkb_prove_batch_submit(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r,
+                           const uint64_t *s);
+int zkb_prove_batch_collect(zkb_ctx *ctx, zkb_proof *out);
+
 /* ---- the generator ---------------------------------------------------------------
  * r1cs_gg_ppzksnark_generator (r1cs_gg_ppzksnark.tcc:211-388) with its secret randomness supplied by the caller,
  * the way zkb_prove takes (r, s): t, alpha, beta, gamma, delta (:221-225, Montgomery Fr) and the two random

@@ -71,6 +71,46 @@ def test_zklaim_batch_of_distinct_witnesses(zctx, ref, zklaim1):
         assert circ.verify(ws[i][: d["num_inputs"]], got[i])
 
 
+def test_pipelined_batches_equal_plain_batches(zctx, ref, zklaim1):
+    """zkb_prove_batch_submit / _collect (inputs of batch k + 1 travel while batch k computes, two staging slots):
+    same proofs as zkb_prove_batch, in submission order; an unsatisfying batch is reported by ITS collect only; a
+    third submit without a collect and a collect with nothing pending are argument errors."""
+    circ, key = zklaim1
+    d = circ.dims()
+    sizes = [3, 1, 4, 2]
+    ws = [np.stack([ref.zklaim_witness(1, 300 + 10 * b + i, d["num_variables"]) for i in range(n)]) for b, n in enumerate(sizes)]
+    rs = [ref.sha512_rng(7000 + b, n) for b, n in enumerate(sizes)]
+    ss = [ref.sha512_rng(8000 + b, n) for b, n in enumerate(sizes)]
+    want = [zctx.prove_batch(key, ws[b], rs[b], ss[b]) for b in range(len(sizes))]
+    got = []
+    zctx.prove_batch_submit(key, ws[0], rs[0], ss[0])
+    for b in range(len(sizes)):
+        if b + 1 < len(sizes):
+            zctx.prove_batch_submit(key, ws[b + 1], rs[b + 1], ss[b + 1])
+        got.append(zctx.prove_batch_collect())
+    def same(a, b):  # as group elements: the Jacobian representative depends on the order pairs reach a bucket
+        return all(np.array_equal(_norm_proof(ref, x), _norm_proof(ref, y)) for x, y in zip(a, b))
+
+    for b in range(len(sizes)):
+        assert got[b].shape == want[b].shape and same(got[b], want[b]), b
+    with pytest.raises(zk.ZkbError) as e:
+        zctx.prove_batch_collect()
+    assert e.value.code == zk.ERR_ARG
+    bad = ws[1].copy()
+    bad[0, d["num_inputs"] + 7] = ws[1][0, d["num_inputs"] + 8] ^ np.uint64(1)
+    zctx.prove_batch_submit(key, ws[0], rs[0], ss[0])
+    zctx.prove_batch_submit(key, bad, rs[1], ss[1])
+    with pytest.raises(zk.ZkbError) as e:
+        zctx.prove_batch_submit(key, ws[1], rs[1], ss[1])  # a third batch before any collect
+    assert e.value.code == zk.ERR_ARG
+    assert same(zctx.prove_batch_collect(), want[0])
+    with pytest.raises(zk.ZkbError) as e:
+        zctx.prove_batch_collect()
+    assert e.value.code == zk.ERR_UNSAT
+    zctx.prove_batch_submit(key, ws[2], rs[2], ss[2])  # the pipeline is usable afterwards
+    assert same(zctx.prove_batch_collect(), want[2])
+
+
 def test_key_tune_keeps_proofs_bit_exact(zctx, ref):
     """zkb_key_tune re-plans the MSM windows from a sample witness: narrower windows for the 0 / 1-dominated
     A / B queries, proofs unchanged (single proof, batch, and a dense witness under the tuned key)."""

@@ -65,6 +65,8 @@ SYMBOLS = {
     "zkb_prove": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _vp, _u64p]),
     "zkb_prove_batch": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p, _vp]),
     "zkb_prove_batch_device": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
+    "zkb_prove_batch_submit": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p]),
+    "zkb_prove_batch_collect": (_i, [_vp, _vp]),
     "zkb_measure_imad_peak": (C.c_double, [_vp, _i]),
     "zkb_profile": (_i, [_vp, _i]),
     "zkb_profile_read": (_i, [_vp, C.POINTER(C.c_double)]),
@@ -376,6 +378,28 @@ class Context:
         """w, r, s are CUDA device pointers (e.g. torch tensors' data_ptr()) on this context's device."""
         out = (Proof * count)()
         self._chk(self.lib.zkb_prove_batch_device(self.h, key.h, count, d_w, d_r, d_s, out))
+        return np.frombuffer(out, dtype=np.uint64).reshape(count, 48).copy()
+
+    def prove_batch_submit(self, key: "Key", w, r, s) -> None:
+        """starts the host-to-device copy of one batch (zkb_prove_batch_submit); at most two batches in flight.
+        The arrays are kept alive here until the matching prove_batch_collect."""
+        w, r, s = _arr(w, 4), _arr(r, 4), _arr(s, 4)
+        count = r.shape[0]
+        assert w.shape[0] == count and s.shape[0] == count
+        self._chk(self.lib.zkb_prove_batch_submit(self.h, key.h, count, w.ctypes.data, r.ctypes.data, s.ctypes.data))
+        self._inflight = getattr(self, "_inflight", [])
+        self._inflight.append((w, r, s, count))
+
+    def prove_batch_collect(self) -> np.ndarray:
+        """proofs of the oldest submitted batch (zkb_prove_batch_collect)"""
+        if not getattr(self, "_inflight", None):
+            raise ZkbError(ERR_ARG, "nothing submitted")
+        count = self._inflight[0][3]
+        out = (Proof * count)()
+        try:
+            self._chk(self.lib.zkb_prove_batch_collect(self.h, out))
+        finally:
+            self._inflight.pop(0)
         return np.frombuffer(out, dtype=np.uint64).reshape(count, 48).copy()
 
     # ---- measurement ------------------------------------------------------------------

@@ -104,6 +104,9 @@ int zkb_init(int device_id, zkb_ctx **out)
     if (cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->side_stream[0], cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->side_stream[1], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_in[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_in[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_join[0], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_join[1], cudaEventDisableTiming) != cudaSuccess ||
@@ -122,6 +125,12 @@ void zkb_shutdown(zkb_ctx *ctx)
     cudaSetDevice(ctx->dev);
     cudaDeviceSynchronize();
     for (auto &s : ctx->scratch) s.release();
+    for (int k = 0; k < 2; k++) {
+        ctx->in_w[k].release();
+        ctx->in_rs[k].release();
+        cudaEventDestroy(ctx->ev_in[k]);
+    }
+    cudaStreamDestroy(ctx->copy_stream);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->prof_pairs_host) {
         cudaFreeHost(ctx->prof_pairs_host);

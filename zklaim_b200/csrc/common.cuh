@@ -48,6 +48,14 @@ struct zkb_ctx {
     uint32_t func_attr_done = 0;            // cudaFuncSetAttribute calls already made on this device (bit per kernel)
     int lane_bias = 0;                      // scratch-slot offset of the active MSM lane
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // pipelined batches (zkb_prove_batch_submit / _collect): inputs of the next batch travel on copy_stream into one of
+    // two staging slots while the current batch computes
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr};
+    zkb::DevBuf in_w[2], in_rs[2];
+    const zkb_key *in_key[2] = {nullptr, nullptr};
+    size_t in_count[2] = {0, 0};
+    int in_head = 0, in_pending = 0;
     std::string err;
     double last_ms = 0.0;
     long launches = 0;

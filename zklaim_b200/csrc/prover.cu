@@ -1009,6 +1009,40 @@ int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64
     return prove_impl(ctx, key, count, w, r, s, false, out, nullptr, false);
 }
 
+int zkb_prove_batch_submit(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r, const uint64_t *s)
+{
+    if (!ctx || !key || !w || !r || !s || !count) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_batch_submit: bad argument");
+    if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_batch_submit: key lives on another device");
+    if (ctx->in_pending >= 2) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_batch_submit: two batches are already in flight, collect one first");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    const int slot = (ctx->in_head + ctx->in_pending) & 1;
+    const size_t wb = count * key->nv * sizeof(Fr), sb = count * sizeof(Fr);
+    ZKB_CUDA(ctx, ctx->in_w[slot].ensure(wb ? wb : 32));
+    ZKB_CUDA(ctx, ctx->in_rs[slot].ensure(2 * sb));
+    if (wb) ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->in_w[slot].p, w, wb, cudaMemcpyHostToDevice, ctx->copy_stream));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->in_rs[slot].p, r, sb, cudaMemcpyHostToDevice, ctx->copy_stream));
+    ZKB_CUDA(ctx, cudaMemcpyAsync((char *)ctx->in_rs[slot].p + sb, s, sb, cudaMemcpyHostToDevice, ctx->copy_stream));
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev_in[slot], ctx->copy_stream));
+    ctx->in_key[slot] = key;
+    ctx->in_count[slot] = count;
+    ctx->in_pending++;
+    return ZKB_OK;
+}
+
+int zkb_prove_batch_collect(zkb_ctx *ctx, zkb_proof *out)
+{
+    if (!ctx || !out) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_batch_collect: bad argument");
+    if (!ctx->in_pending) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_batch_collect: nothing submitted");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    const int slot = ctx->in_head;
+    const size_t count = ctx->in_count[slot];
+    ctx->in_head ^= 1; // the slot is released whatever happens below: prove_impl returns with the device idle
+    ctx->in_pending--;
+    ZKB_CUDA(ctx, cudaStreamWaitEvent(ctx->main_stream, ctx->ev_in[slot], 0));
+    const uint64_t *dw = (const uint64_t *)ctx->in_w[slot].p, *dr = (const uint64_t *)ctx->in_rs[slot].p;
+    return prove_impl(ctx, ctx->in_key[slot], count, dw, dr, dr + count * 4, true, out, nullptr, false);
+}
+
 int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const void *d_w, const void *d_r, const void *d_s,
                            zkb_proof *out)
 {
