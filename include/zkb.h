@@ -252,6 +252,28 @@ typedef struct {
 } zkb_setup_out;
 int zkb_setup(zkb_ctx *ctx, const zkb_setup_desc *desc, zkb_setup_out *out, int *swapped);
 
+/* ---- verifier side: pairings and batch verification ---------------------- */
+/* alt_bn128_ate_miller_loop(precompute_G1(P), precompute_G2(Q)) (reduced = 0) or alt_bn128_reduced_pairing(P, Q)
+ * (reduced = 1) for n affine pairs (libff/algebra/curves/alt_bn128/alt_bn128_pairing.cpp:371-420, 523-533).
+ * out: n x 12 Fq (48 limbs each) in libff's member order c0.c0.c0, c0.c0.c1, c0.c1.c0, ... c1.c2.c1 --
+ * bit-identical to the reference's alt_bn128_Fq12 / alt_bn128_GT. */
+int zkb_pairing(zkb_ctx *ctx, const uint64_t *g1_affine, const uint64_t *g2_affine, size_t n, int reduced, uint64_t *out);
+
+/* r1cs_gg_ppzksnark_verification_key (r1cs_gg_ppzksnark.hpp:159-216) as flat host arrays */
+typedef struct zkb_vk_desc {
+    const uint64_t *alpha_g1_beta_g2; /* 48 limbs: the GT element e(alpha, beta), member order as zkb_pairing */
+    const uint64_t *gamma_g2;         /* 16 limbs, affine */
+    const uint64_t *delta_g2;         /* 16 limbs, affine */
+    const uint64_t *gamma_ABC_g1;     /* (num_inputs + 1) x 8 limbs, affine: accumulation_vector first, then rest */
+    uint64_t num_inputs;
+} zkb_vk_desc;
+/* r1cs_gg_ppzksnark_verifier_strong_IC (r1cs_gg_ppzksnark.tcc:523-622, reached from libsnark_verify,
+ * zklaim/libsnark_wrapper.cpp:252-276) for n proofs under one key.  primary: n x num_inputs Fr (Montgomery);
+ * proofs: n x 48 limbs in the layout zkb_prove writes (A 12, B 24, C 12: Jacobian).  accept[i] = 1 when the
+ * reference verifier returns true for proof i, else 0 (a point off its curve, or the pairing equation failing). */
+int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primary, const uint64_t *proofs, size_t n,
+                     int32_t *accept);
+
 /* ---- measurement helpers (used by bench.py only) ------------------------------------ */
 /* Sustained integer multiply-add rate of the device, measured with chains of dependent Fq Montgomery
  * products (136 multiply-adds of 32 x 32 + 64 -> 64 bits each, the instruction mix of every kernel here) on

@@ -1029,6 +1029,30 @@ size_t zkref_proof_serialize(const u64 *proof, unsigned char *out, size_t cap)
     return s.size();
 }
 
+/* ---- pairing (verifier side) ---------------------------------------------- */
+static void st_fq12(u64 *p, const libff::alt_bn128_Fq12 &f)
+{
+    const libff::alt_bn128_Fq6 *h[2] = {&f.c0, &f.c1};
+    for (int i = 0; i < 2; i++) {
+        st2(p + 24 * i, h[i]->c0);
+        st2(p + 24 * i + 8, h[i]->c1);
+        st2(p + 24 * i + 16, h[i]->c2);
+    }
+}
+/* alt_bn128_ate_miller_loop (reduced = 0) or alt_bn128_reduced_pairing (reduced = 1) of affine P, Q
+ * (alt_bn128_pairing.cpp:371-420, 523-533); out: 12 Fq = c0.c0.c0, c0.c0.c1, c0.c1.c0, ... c1.c2.c1 */
+void zkref_pairing(const u64 *g1_affine, const u64 *g2_affine, int reduced, u64 *out48)
+{
+    zkref_init();
+    const G1T P = ld_g1_affine(g1_affine);
+    const G2T Q = ld_g2_affine(g2_affine);
+    libff::alt_bn128_Fq12 f = PP::miller_loop(PP::precompute_G1(P), PP::precompute_G2(Q));
+    if (reduced) f = PP::final_exponentiation(f);
+    st_fq12(out48, f);
+}
+/* vk.alpha_g1_beta_g2 (r1cs_gg_ppzksnark.tcc:338) of the circuit's key */
+void zkref_vk_alpha_beta(void *h, u64 *out48) { st_fq12(out48, ((Circuit *)h)->vk.alpha_g1_beta_g2); }
+
 /* ---- the zklaim C bridge, reference flavour (libsnark_wrapper.cpp:195-276) --------- */
 /* Runs libsnark_trusted_setup / libsnark_prove / libsnark_verify of the reference on a
  * k-payload credential; returns prove seconds incl. the per-call key import, or < 0. */

@@ -66,6 +66,8 @@ _SIG = {
     "zkref_verify": (_i, [_vp, _vp, _vp]),
     "zkref_proof_serialize": (_sz, [_vp, _vp, _sz]),
     "zkref_bridge_roundtrip": (_d, [_sz, _u64, C.POINTER(_i)]),
+    "zkref_pairing": (None, [_vp, _vp, _i, _vp]),
+    "zkref_vk_alpha_beta": (None, [_vp, _vp]),
 }
 
 
@@ -272,6 +274,12 @@ class Circuit:
         self.L.zkref_vk_export(self.h, g.ctypes.data, d.ctypes.data, abc.ctypes.data)
         return {"gamma_g2": g, "delta_g2": d, "gamma_ABC_g1": abc}
 
+    def vk_alpha_beta(self) -> np.ndarray:
+        """vk.alpha_g1_beta_g2 as 12 Fq (48 limbs, libff member order)"""
+        out = np.zeros(48, dtype=np.uint64)
+        self.L.zkref_vk_alpha_beta(self.h, out.ctypes.data)
+        return out
+
     def import_vk(self, alpha_g1, beta_g2, gamma_g2, delta_g2, gamma_abc):
         a, b, g, d, abc = _u(alpha_g1), _u(beta_g2), _u(gamma_g2), _u(delta_g2), _u(gamma_abc, 8)
         self.L.zkref_vk_import(self.h, a.ctypes.data, b.ctypes.data, g.ctypes.data, d.ctypes.data, abc.ctypes.data, len(abc))
@@ -333,6 +341,15 @@ class Circuit:
     def verify(self, primary, proof) -> bool:
         p, pr = _u(primary, 4), _u(proof)
         return bool(self.L.zkref_verify(self.h, p.ctypes.data, pr.ctypes.data))
+
+
+def pairing(g1_affine, g2_affine, reduced: bool = True) -> np.ndarray:
+    """libff's alt_bn128_ate_miller_loop / alt_bn128_reduced_pairing of one affine pair -> 48 limbs"""
+    p, q = _u(g1_affine), _u(g2_affine)
+    assert p.size == 8 and q.size == 16
+    out = np.zeros(48, dtype=np.uint64)
+    lib().zkref_pairing(p.ctypes.data, q.ctypes.data, int(reduced), out.ctypes.data)
+    return out
 
 
 def proof_bytes(proof) -> bytes:

@@ -125,10 +125,59 @@ def provers():
         c.free()
 
 
+def pairings():
+    """alt_bn128_ate_miller_loop / alt_bn128_reduced_pairing (alt_bn128_pairing.cpp:371-420, 523-533) on seeded points,
+    incl. the degenerate input the reference accepts (P at infinity enters the loop as (0, 1))."""
+    n = 6
+    P = zkref.bases(G1, (1 << 42) + 1, n, mt=False)
+    Q = zkref.bases(G2, (1 << 42) + 2, n, mt=False)
+    P[4] = 0  # (Q at infinity trips an assert of the reference, alt_bn128_pairing.cpp:348: not a defined input)
+    d = {"P": P, "Q": Q,
+         "miller": np.stack([zkref.pairing(P[i], Q[i], False) for i in range(n)]),
+         "reduced": np.stack([zkref.pairing(P[i], Q[i], True) for i in range(n)])}
+    np.savez_compressed(os.path.join(OUT, "pairing.npz"), **d)
+
+
+def verifier():
+    """r1cs_gg_ppzksnark_verifier_strong_IC (r1cs_gg_ppzksnark.tcc:523-622) decisions on valid and tampered proofs."""
+    nc, ni = 37, 5
+    c = zkref.Circuit.example(nc, ni, seed=nc)
+    c.setup()
+    vk = c.export_vk()
+    w = c.witness()
+    proofs, primary = [], []
+    for k in range(4):
+        out = c.prove(w, zkref.sha512_rng(500 + k, 1)[0], zkref.sha512_rng(600 + k, 1)[0], want_H=False)
+        proofs.append(np.asarray(out["proof"], dtype=np.uint64).reshape(48))
+        primary.append(w[:ni].copy())
+    # Jacobian representatives with Z != 1 must be accepted as well: proof 1 keeps the prover's raw output
+    norm = np.concatenate([zkref.to_affine_jac(G1, proofs[0][None, :12])[0], zkref.to_affine_jac(G2, proofs[0][None, 12:36])[0],
+                           zkref.to_affine_jac(G1, proofs[0][None, 36:])[0]])
+    proofs[0] = norm
+    t = proofs[2].copy()                      # C of another proof: pairing equation fails
+    t[36:] = proofs[3][36:]
+    proofs.append(t); primary.append(w[:ni].copy())
+    t = norm.copy()                           # A off the curve
+    t[0] ^= np.uint64(1)
+    proofs.append(t); primary.append(w[:ni].copy())
+    x = w[:ni].copy()                         # wrong public input
+    x[2] = zkref.sha512_rng(9, 1)[0]
+    proofs.append(proofs[1].copy()); primary.append(x)
+    t = norm.copy()                           # A = zero (well formed, equation fails)
+    t[:12] = zkref.group_op(G1, 0, norm[None, :12], zkref.group_op(G1, 3, norm[None, :12]))[0]
+    proofs.append(t); primary.append(w[:ni].copy())
+    proofs, primary = np.stack(proofs), np.stack(primary)
+    accept = np.array([c.verify(primary[i], proofs[i]) for i in range(len(proofs))], dtype=np.int32)
+    assert accept.tolist() == [1, 1, 1, 1, 0, 0, 0, 0], accept
+    d = {"alpha_g1_beta_g2": c.vk_alpha_beta(), "gamma_g2": vk["gamma_g2"], "delta_g2": vk["delta_g2"],
+         "gamma_ABC_g1": vk["gamma_ABC_g1"], "primary": primary, "proofs": proofs, "accept": accept}
+    np.savez_compressed(os.path.join(OUT, "verify.npz"), **d)
+    c.free()
+
+
 if __name__ == "__main__":
-    fields()
-    groups()
-    domains()
-    provers()
+    which = sys.argv[1:] or ["fields", "groups", "domains", "provers", "pairings", "verifier"]
+    for name in which:
+        globals()[name]()
     print("golden vectors written to", OUT)
     os.system(f"ls -la {OUT}")

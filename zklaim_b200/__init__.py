@@ -67,6 +67,8 @@ SYMBOLS = {
     "zkb_prove_batch_device": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
     "zkb_prove_batch_submit": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p]),
     "zkb_prove_batch_collect": (_i, [_vp, _vp]),
+    "zkb_pairing": (_i, [_vp, _u64p, _u64p, _sz, _i, _u64p]),
+    "zkb_verify_batch": (_i, [_vp, _vp, _u64p, _u64p, _sz, _vp]),
     "zkb_measure_imad_peak": (C.c_double, [_vp, _i]),
     "zkb_profile": (_i, [_vp, _i]),
     "zkb_profile_read": (_i, [_vp, C.POINTER(C.c_double)]),
@@ -123,6 +125,13 @@ class _KeyDesc(C.Structure):
         ("A_query", C.c_void_p), ("B_nnz", C.c_size_t), ("B_index", C.c_void_p),
         ("B_g1", C.c_void_p), ("B_g2", C.c_void_p),
         ("H_size", C.c_size_t), ("H_query", C.c_void_p), ("L_query", C.c_void_p),
+    ]
+
+
+class _VkDesc(C.Structure):
+    _fields_ = [
+        ("alpha_g1_beta_g2", C.c_void_p), ("gamma_g2", C.c_void_p), ("delta_g2", C.c_void_p),
+        ("gamma_ABC_g1", C.c_void_p), ("num_inputs", C.c_uint64),
     ]
 
 
@@ -414,6 +423,34 @@ class Context:
         self._chk(self.lib.zkb_profile_read(self.h, out))
         return {"g1_ms": out[0], "g1_launches": int(out[1]), "g1_pairs": out[2],
                 "g2_ms": out[3], "g2_launches": int(out[4]), "g2_pairs": out[5]}
+
+    # ---- verifier side -------------------------------------------------------------------
+    def pairing(self, g1_affine, g2_affine, reduced: bool = True) -> np.ndarray:
+        """alt_bn128_ate_miller_loop / alt_bn128_reduced_pairing (alt_bn128_pairing.cpp:371-420, 523-533) of n affine
+        pairs -> (n, 48) limbs, bit-identical to libff's Fq12"""
+        p = _arr(g1_affine, 8).reshape(-1, 8)
+        q = _arr(g2_affine, 16).reshape(-1, 16)
+        assert len(p) == len(q)
+        out = np.zeros((len(p), 48), dtype=np.uint64)
+        self._chk(self.lib.zkb_pairing(self.h, p.ctypes.data, q.ctypes.data, len(p), int(reduced), out.ctypes.data))
+        return out
+
+    def verify_batch(self, vk: dict, primary, proofs) -> np.ndarray:
+        """r1cs_gg_ppzksnark_verifier_strong_IC (r1cs_gg_ppzksnark.tcc:523-622) for n proofs under one key.
+        vk: alpha_g1_beta_g2 (48), gamma_g2 (16), delta_g2 (16), gamma_ABC_g1 (ni + 1, 8); primary (n, ni, 4);
+        proofs (n, 48) as zkb_prove writes them.  Returns n booleans."""
+        ab = _arr(vk["alpha_g1_beta_g2"], 48)
+        g, d = _arr(vk["gamma_g2"], 16), _arr(vk["delta_g2"], 16)
+        abc = _arr(vk["gamma_ABC_g1"], 8).reshape(-1, 8)
+        ni = len(abc) - 1
+        pr = _arr(proofs, 48).reshape(-1, 48)
+        n = len(pr)
+        x = _arr(primary, 4).reshape(n, ni, 4) if ni else np.zeros((n, 0, 4), dtype=np.uint64)
+        desc = _VkDesc(ab.ctypes.data, g.ctypes.data, d.ctypes.data, abc.ctypes.data, ni)
+        acc = np.zeros(n, dtype=np.int32)
+        self._chk(self.lib.zkb_verify_batch(self.h, C.byref(desc), x.ctypes.data if ni else None, pr.ctypes.data, n,
+                                            acc.ctypes.data))
+        return acc.astype(bool)
 
     def last_device_ms(self) -> float:
         return float(self.lib.zkb_last_device_ms(self.h))

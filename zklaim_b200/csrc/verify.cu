@@ -1,0 +1,227 @@
+// verify.cu -- batch Groth16 verification on the GPU.
+//
+// Replaces, for a batch of proofs under one verification key, the reference's
+//   r1cs_gg_ppzksnark_verifier_strong_IC / _online_verifier_weak_IC
+//       (libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.tcc:523-622)
+//   accumulation_vector::accumulate_chunk (libsnark/common/data_structures/accumulation_vector.tcc:75-118)
+//   alt_bn128_pp::miller_loop / double_miller_loop / final_exponentiation (alt_bn128_pairing.cpp:109-500)
+// reached from libsnark_verify (zklaim/libsnark_wrapper.cpp:252-276).  Per proof the same decision as the
+// reference, from the same values: QAP = FE(ML(A, B) * conj(ML(acc, gamma) * ML(C, delta))) compared with
+// vk.alpha_g1_beta_g2 limb for limb, AND the three proof points lying on their curves.
+//
+// Parallel shape: the batch is the parallel axis.  Every Miller loop has the same control flow (the loop
+// count is a constant), so the 3 n Miller loops of n proofs run in lock step, one per lane; the n final
+// exponentiations likewise.  The public-input sums input_j * gamma_ABC[j + 1] are one lane per (proof, input).
+// Latency-bound (dependent 254-bit products): built with the out-of-line multiplier.
+#define ZKB_NOINLINE_MUL 1
+#include "common.cuh"
+#include "pairing.cuh"
+
+#include <mutex>
+
+using namespace zkb;
+
+namespace {
+enum { SV_CONST = 58, SV_IN, SV_T, SV_F, SV_OUT }; // scratch slots of this file (prover.cu ends at 57)
+
+// affine limbs at the ABI: all-zero = infinity (zkb.h conventions)
+template <class F> __device__ void affine_in(const Affine<F> &a, F &x, F &y)
+{
+    if (a.is_inf()) {
+        x = F::zero();
+        y = F::one();
+    } else {
+        x = a.x;
+        y = a.y;
+    }
+}
+
+__device__ Fq2 twist_b_of(const PairingConsts &K) { return K.twist_b; }
+
+// lane t = (proof i, input j): T = input_j * gamma_ABC[j + 1]
+__global__ void k_vf_inputs(const Fr *primary, const G1Affine *gamma_abc, G1X *T, uint32_t n, uint32_t ni)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * ni) return;
+    const uint32_t j = t % ni;
+    const Fr k = ld_vec(primary + t).from_mont();
+    st_vec(T + t, scalar_mul<Fq>(k.v, G1X::from_affine(ld_vec(gamma_abc + j + 1))));
+}
+
+struct ProofJ { // zkb_proof_out layout
+    G1J A;
+    G2J B;
+    G1J C;
+};
+
+// lane t = which * n + i: Miller loop `which` of proof i (0: (A, B), 1: (acc, gamma), 2: (C, delta)); also the
+// well-formedness bits of the points this lane touches
+__global__ void k_vf_miller(const ProofJ *proofs, const G1X *T, const G1Affine *gamma_abc, const G2Affine *gamma_g2,
+                            const G2Affine *delta_g2, const PairingConsts *Kp, Fq12 *F, uint32_t *wf, uint32_t n, uint32_t ni)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 3 * n) return;
+    const uint32_t which = t / n, i = t % n;
+    const PairingConsts &K = *Kp;
+    Fq px, py;
+    Fq2 qx, qy;
+    bool ok = true;
+    if (which == 0) {
+        const G1J A = ld_vec(&proofs[i].A);
+        const G2J B = ld_vec(&proofs[i].B);
+        Fq three = Fq::one();
+        three = three + three.dbl();
+        ok = jacobian_well_formed<Fq>(A.X, A.Y, A.Z, three) && jacobian_well_formed<Fq2>(B.X, B.Y, B.Z, twist_b_of(K));
+        jac_to_affine<Fq>(A, px, py);
+        jac_to_affine<Fq2>(B, qx, qy);
+    } else if (which == 1) {
+        G1X acc = G1X::from_affine(ld_vec(gamma_abc));
+        for (uint32_t j = 0; j < ni; j++) acc.add(ld_vec(T + (size_t)i * ni + j));
+        jac_to_affine<Fq>(acc.to_jacobian(), px, py);
+        affine_in<Fq2>(ld_vec(gamma_g2), qx, qy);
+    } else {
+        const G1J C = ld_vec(&proofs[i].C);
+        Fq three = Fq::one();
+        three = three + three.dbl();
+        ok = jacobian_well_formed<Fq>(C.X, C.Y, C.Z, three);
+        jac_to_affine<Fq>(C, px, py);
+        affine_in<Fq2>(ld_vec(delta_g2), qx, qy);
+    }
+    wf[t] = ok ? 1u : 0u;
+    st_vec(F + t, miller_loop(px, py, qx, qy, K));
+}
+
+// lane i: the decision for proof i
+__global__ void k_vf_final(const Fq12 *F, const uint32_t *wf, const Fq12 *alpha_beta, const PairingConsts *Kp, int32_t *accept, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const bool eq = groth16_pairing_check(ld_vec(F + i), ld_vec(F + n + i), ld_vec(F + 2 * n + i), ld_vec(alpha_beta), *Kp);
+    const bool ok = wf[i] && wf[2 * n + i] && eq;
+    accept[i] = ok ? 1 : 0;
+}
+
+// lane i: alt_bn128_ate_miller_loop / alt_bn128_reduced_pairing of one affine pair
+__global__ void k_pairing(const G1Affine *P, const G2Affine *Q, const PairingConsts *Kp, int reduced, Fq12 *out, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fq px, py;
+    Fq2 qx, qy;
+    affine_in<Fq>(ld_vec(P + i), px, py);
+    affine_in<Fq2>(ld_vec(Q + i), qx, qy);
+    Fq12 f = miller_loop(px, py, qx, qy, *Kp);
+    if (reduced) f = final_exponentiation(f, *Kp);
+    st_vec(out + i, f);
+}
+
+const PairingConsts &host_consts()
+{
+    static PairingConsts K;
+    static std::once_flag once;
+    std::call_once(once, [] { pairing_consts_init(K); });
+    return K;
+}
+
+int consts_on_device(zkb_ctx *ctx, const PairingConsts **out)
+{
+    DevBuf &b = ctx->scratch[SV_CONST];
+    if (!b.p) {
+        ZKB_CUDA(ctx, b.ensure(sizeof(PairingConsts)));
+        // the source is a process-lifetime static: a stream-ordered copy from it is safe
+        ZKB_CUDA(ctx, cudaMemcpyAsync(b.p, &host_consts(), sizeof(PairingConsts), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    *out = b.as<PairingConsts>();
+    return ZKB_OK;
+}
+
+constexpr int LANES = 32; // one warp per block: the lanes of a warp run identical instruction streams
+} // namespace
+
+extern "C" {
+
+int zkb_pairing(zkb_ctx *ctx, const uint64_t *g1_affine, const uint64_t *g2_affine, size_t n, int reduced, uint64_t *out)
+{
+    if (!ctx || !g1_affine || !g2_affine || !out) return fail(ctx, ZKB_ERR_ARG, "zkb_pairing: bad argument");
+    if (n == 0) return ZKB_OK;
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    const PairingConsts *K;
+    int rc = consts_on_device(ctx, &K);
+    if (rc) return rc;
+    const size_t in_bytes = n * (sizeof(G1Affine) + sizeof(G2Affine));
+    ZKB_CUDA(ctx, ctx->scratch[SV_IN].ensure(in_bytes));
+    ZKB_CUDA(ctx, ctx->scratch[SV_F].ensure(n * sizeof(Fq12)));
+    if (ensure_pinned(ctx, n * sizeof(Fq12))) return ZKB_ERR_CUDA;
+    G2Affine *dQ = ctx->scratch[SV_IN].as<G2Affine>();
+    G1Affine *dP = (G1Affine *)(dQ + n);
+    ZKB_CUDA(ctx, cudaMemcpyAsync(dQ, g2_affine, n * sizeof(G2Affine), cudaMemcpyHostToDevice, ctx->stream));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(dP, g1_affine, n * sizeof(G1Affine), cudaMemcpyHostToDevice, ctx->stream));
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    k_pairing<<<ceil_div(n, LANES), LANES, 0, ctx->stream>>>(dP, dQ, K, reduced, ctx->scratch[SV_F].as<Fq12>(), (uint32_t)n);
+    ZKB_LAUNCH_CHECK(ctx);
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, ctx->scratch[SV_F].p, n * sizeof(Fq12), cudaMemcpyDeviceToHost, ctx->stream));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_ms = ms;
+    memcpy(out, ctx->pinned, n * sizeof(Fq12));
+    return ZKB_OK;
+}
+
+int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primary, const uint64_t *proofs, size_t n, int32_t *accept)
+{
+    if (!ctx || !vk || !proofs || !accept || !vk->alpha_g1_beta_g2 || !vk->gamma_g2 || !vk->delta_g2 || !vk->gamma_ABC_g1 ||
+        (!primary && vk->num_inputs))
+        return fail(ctx, ZKB_ERR_ARG, "zkb_verify_batch: bad argument");
+    if (n == 0) return ZKB_OK;
+    if (n > (1u << 24) || vk->num_inputs > (1u << 24)) return fail(ctx, ZKB_ERR_ARG, "zkb_verify_batch: batch too large");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    const PairingConsts *K;
+    int rc = consts_on_device(ctx, &K);
+    if (rc) return rc;
+    const uint32_t ni = (uint32_t)vk->num_inputs, nn = (uint32_t)n;
+    // one staging buffer: alpha_beta | gamma_g2 | delta_g2 | gamma_ABC | proofs | primary   (all multiples of 16 bytes)
+    const size_t o_ab = 0, o_g = o_ab + sizeof(Fq12), o_d = o_g + sizeof(G2Affine), o_abc = o_d + sizeof(G2Affine);
+    const size_t o_pr = o_abc + (size_t)(ni + 1) * sizeof(G1Affine), o_in = o_pr + n * sizeof(ProofJ);
+    const size_t total = o_in + n * (size_t)ni * sizeof(Fr);
+    static_assert(sizeof(ProofJ) == 48 * 8, "zkb_proof_out layout");
+    ZKB_CUDA(ctx, ctx->scratch[SV_IN].ensure(total));
+    ZKB_CUDA(ctx, ctx->scratch[SV_T].ensure((size_t)nn * (ni ? ni : 1) * sizeof(G1X)));
+    ZKB_CUDA(ctx, ctx->scratch[SV_F].ensure(3 * n * sizeof(Fq12)));
+    ZKB_CUDA(ctx, ctx->scratch[SV_OUT].ensure(4 * n * sizeof(uint32_t)));
+    if (ensure_pinned(ctx, n * sizeof(int32_t))) return ZKB_ERR_CUDA;
+    char *base = ctx->scratch[SV_IN].as<char>();
+    cudaStream_t st = ctx->stream;
+    ZKB_CUDA(ctx, cudaMemcpyAsync(base + o_ab, vk->alpha_g1_beta_g2, sizeof(Fq12), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(base + o_g, vk->gamma_g2, sizeof(G2Affine), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(base + o_d, vk->delta_g2, sizeof(G2Affine), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(base + o_abc, vk->gamma_ABC_g1, (size_t)(ni + 1) * sizeof(G1Affine), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(base + o_pr, proofs, n * sizeof(ProofJ), cudaMemcpyHostToDevice, st));
+    if (ni) ZKB_CUDA(ctx, cudaMemcpyAsync(base + o_in, primary, n * (size_t)ni * sizeof(Fr), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+    const G1Affine *d_abc = (const G1Affine *)(base + o_abc);
+    G1X *dT = ctx->scratch[SV_T].as<G1X>();
+    Fq12 *dF = ctx->scratch[SV_F].as<Fq12>();
+    uint32_t *d_wf = ctx->scratch[SV_OUT].as<uint32_t>();
+    int32_t *d_acc = (int32_t *)(d_wf + 3 * n);
+    if (ni) {
+        k_vf_inputs<<<ceil_div((size_t)nn * ni, LANES), LANES, 0, st>>>((const Fr *)(base + o_in), d_abc, dT, nn, ni);
+        ZKB_LAUNCH_CHECK(ctx);
+    }
+    k_vf_miller<<<ceil_div(3 * n, LANES), LANES, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
+                                                        (const G2Affine *)(base + o_d), K, dF, d_wf, nn, ni);
+    ZKB_LAUNCH_CHECK(ctx);
+    k_vf_final<<<ceil_div(n, LANES), LANES, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
+    ZKB_LAUNCH_CHECK(ctx);
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_acc, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_ms = ms;
+    memcpy(accept, ctx->pinned, n * sizeof(int32_t));
+    return ZKB_OK;
+}
+
+} // extern "C"
