@@ -267,6 +267,92 @@ inline libsnark::r1cs_gg_ppzksnark_proof<PP> wrap_proof(const zkb_proof &p)
     return libsnark::r1cs_gg_ppzksnark_proof<PP>(std::move(A), std::move(B), std::move(C));
 }
 
+/* ---- verifier side -------------------------------------------------------------------------------- */
+/* r1cs_gg_ppzksnark_verification_key (r1cs_gg_ppzksnark.hpp:159-216) as the flat arrays of zkb_vk_desc */
+struct VkArrays {
+    uint64_t alpha_beta[48], gamma_g2[16], delta_g2[16];
+    std::vector<uint64_t> gamma_abc;
+    zkb_vk_desc desc;
+};
+inline void put_fq12(uint64_t *dst, const libff::alt_bn128_Fq12 &f)
+{
+    const libff::alt_bn128_Fq6 *h[2] = {&f.c0, &f.c1};
+    for (int i = 0; i < 2; i++) {
+        const libff::alt_bn128_Fq2 *c[3] = {&h[i]->c0, &h[i]->c1, &h[i]->c2};
+        for (int j = 0; j < 3; j++) {
+            put_fp(dst + 24 * i + 8 * j, c[j]->c0);
+            put_fp(dst + 24 * i + 8 * j + 4, c[j]->c1);
+        }
+    }
+}
+inline void pack_verification_key(const libsnark::r1cs_gg_ppzksnark_verification_key<PP> &vk, VkArrays &a)
+{
+    put_fq12(a.alpha_beta, vk.alpha_g1_beta_g2);
+    put_g2_affine(a.gamma_g2, vk.gamma_g2);
+    put_g2_affine(a.delta_g2, vk.delta_g2);
+    /* accumulation_vector: `first`, then the sparse `rest` over the domain 0 .. num_inputs - 1 (absent index = zero) */
+    const size_t ni = vk.gamma_ABC_g1.rest.domain_size();
+    a.gamma_abc.assign(8 * (ni + 1), 0);
+    put_g1_affine(&a.gamma_abc[0], vk.gamma_ABC_g1.first);
+    for (size_t k = 0; k < vk.gamma_ABC_g1.rest.indices.size(); k++)
+        put_g1_affine(&a.gamma_abc[8 * (vk.gamma_ABC_g1.rest.indices[k] + 1)], vk.gamma_ABC_g1.rest.values[k]);
+    a.desc.alpha_g1_beta_g2 = a.alpha_beta;
+    a.desc.gamma_g2 = a.gamma_g2;
+    a.desc.delta_g2 = a.delta_g2;
+    a.desc.gamma_ABC_g1 = a.gamma_abc.data();
+    a.desc.num_inputs = ni;
+}
+inline void pack_proof(const libsnark::r1cs_gg_ppzksnark_proof<PP> &pr, uint64_t *dst /* 48 limbs */)
+{
+    const libff::alt_bn128_Fq *g1[2][3] = {{&pr.g_A.X, &pr.g_A.Y, &pr.g_A.Z}, {&pr.g_C.X, &pr.g_C.Y, &pr.g_C.Z}};
+    for (int k = 0; k < 3; k++) {
+        put_fp(dst + 4 * k, *g1[0][k]);
+        put_fp(dst + 36 + 4 * k, *g1[1][k]);
+    }
+    const libff::alt_bn128_Fq2 *g2[3] = {&pr.g_B.X, &pr.g_B.Y, &pr.g_B.Z};
+    for (int k = 0; k < 3; k++) {
+        put_fp(dst + 12 + 8 * k, g2[k]->c0);
+        put_fp(dst + 12 + 8 * k + 4, g2[k]->c1);
+    }
+}
+/* n proofs under one key: the decisions of r1cs_gg_ppzksnark_verifier_strong_IC (r1cs_gg_ppzksnark.tcc:612-622), which
+ * rejects an input of the wrong length before any pairing work */
+inline std::vector<bool> verifier_strong_IC_batch(const libsnark::r1cs_gg_ppzksnark_verification_key<PP> &vk,
+                                                  const std::vector<std::vector<FrT>> &inputs,
+                                                  const std::vector<libsnark::r1cs_gg_ppzksnark_proof<PP>> &proofs)
+{
+    if (inputs.size() != proofs.size()) throw std::runtime_error("verifier_strong_IC_batch: inputs / proofs differ in number");
+    VkArrays a;
+    pack_verification_key(vk, a);
+    const size_t ni = a.desc.num_inputs, n = proofs.size();
+    std::vector<bool> res(n, false);
+    std::vector<size_t> live;
+    for (size_t i = 0; i < n; i++)
+        if (inputs[i].size() == ni) live.push_back(i);
+    if (live.empty()) return res;
+    std::vector<uint64_t> x(live.size() * ni * 4 + 4), pr(live.size() * 48);
+    for (size_t k = 0; k < live.size(); k++) {
+        for (size_t j = 0; j < ni; j++) put_fr(&x[(k * ni + j) * 4], inputs[live[k]][j]);
+        pack_proof(proofs[live[k]], &pr[48 * k]);
+    }
+    std::vector<int32_t> acc(live.size(), 0);
+    zkb_ctx *ctx = Session::get().ctx();
+    const int rc = zkb_verify_batch(ctx, &a.desc, x.data(), pr.data(), live.size(), acc.data());
+    if (rc != ZKB_OK) throw std::runtime_error(std::string("zkb_verify_batch failed: ") + zkb_last_error(ctx));
+    for (size_t k = 0; k < live.size(); k++) res[live[k]] = acc[k] != 0;
+    return res;
+}
+/* Drop-in for r1cs_gg_ppzksnark_verifier_strong_IC<alt_bn128_pp> (r1cs_gg_ppzksnark.tcc:612-622; called from
+ * verify_proof, zklaim/snark.cpp:53-63). */
+template <typename ppT>
+bool verifier_strong_IC(const libsnark::r1cs_gg_ppzksnark_verification_key<ppT> &vk,
+                        const libsnark::r1cs_gg_ppzksnark_primary_input<ppT> &primary_input,
+                        const libsnark::r1cs_gg_ppzksnark_proof<ppT> &proof)
+{
+    static_assert(std::is_same<ppT, PP>::value, "the zkb backend implements alt_bn128 only");
+    return verifier_strong_IC_batch(vk, {primary_input}, {proof})[0];
+}
+
 /* full variable assignment as the contiguous limb array zkb_prove expects (Fp_model is 32 bytes, fp.hpp:42) */
 inline void pack_assignment(const std::vector<FrT> &primary, const std::vector<FrT> &auxiliary, uint64_t *dst)
 {

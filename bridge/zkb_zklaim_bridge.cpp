@@ -245,6 +245,42 @@ int zkb_libsnark_prove_batch(zklaim_ctx **ctxs, size_t n)
     }
 }
 
+/* Replacement of libsnark_verify (zklaim/zklaim.h:262, libsnark_wrapper.cpp:252-276) for `n` credentials that share one
+ * verification key: keys and proofs are parsed by the reference's own importers, the public input is the reference's
+ * zklaim_input_map (zklaim_gadget.cpp:116), the pairing work runs on the GPU.  results[i] = libsnark_verify's return
+ * value for credential i (0 = accepted, 1 = rejected); returns 0, or < 0 when the call itself failed. */
+int zkb_libsnark_verify_batch(zklaim_ctx **ctxs, size_t n, int *results)
+{
+    if (!n) return 0;
+    StdoutMute mute;
+    ppT::init_public_params();
+    try {
+        r1cs_gg_ppzksnark_verification_key<ppT> vk;
+        libsnark_import_vk(&vk, ctxs[0]->vk, ctxs[0]->vk_size);
+        std::vector<std::vector<FrT>> inputs(n);
+        std::vector<r1cs_gg_ppzksnark_proof<ppT>> proofs(n);
+        for (size_t i = 0; i < n; i++) {
+            if (ctxs[i]->vk_size != ctxs[0]->vk_size || memcmp(ctxs[i]->vk, ctxs[0]->vk, ctxs[0]->vk_size)) return -2;
+            libsnark_import_proof(&proofs[i], ctxs[i]->proof, ctxs[i]->proof_size);
+            inputs[i] = zklaim_input_map<FrT>(ctxs[i]);
+        }
+        const std::vector<bool> ok = zkb_bridge::verifier_strong_IC_batch(vk, inputs, proofs);
+        for (size_t i = 0; i < n; i++) results[i] = ok[i] ? 0 : 1;
+        return 0;
+    } catch (const std::exception &e) {
+        fprintf(stderr, "zkb_libsnark_verify_batch: %s\n", e.what());
+        return -1;
+    }
+}
+
+/* Replacement of libsnark_verify for one credential: 0 = accepted. */
+int zkb_libsnark_verify(zklaim_ctx *ctx)
+{
+    int res = 1;
+    const int rc = zkb_libsnark_verify_batch(&ctx, 1, &res);
+    return rc ? rc : res;
+}
+
 void zkb_bridge_reset(void)
 {
     g_keys_by_pk_hash.clear();
@@ -441,6 +477,47 @@ int zkbr_roundtrip(void *h, size_t count, uint64_t seed0, double *seconds)
     for (size_t i = 0; i < count; i++) ok += libsnark_verify(ptrs[i]) == 0 ? 1 : 0;
     seconds[1] = now_s() - t;
     return ok;
+}
+
+/* `count` credentials -> zkb_libsnark_prove_batch; credential `tamper` (if < count) gets the proof of its neighbour;
+ * then BOTH verifiers: the reference's libsnark_verify per credential and zkb_libsnark_verify_batch.  Returns the
+ * number of credentials on which the two agree (must be `count`), < 0 on failure; accepted[0] = how many the GPU
+ * verifier accepted; seconds[0] = reference verify wall time, seconds[1] = GPU batch verify wall time. */
+int zkbr_verify_roundtrip(void *h, size_t count, uint64_t seed0, size_t tamper, int *accepted, double *seconds)
+{
+    Bench *b = (Bench *)h;
+    std::vector<std::unique_ptr<Credential>> creds;
+    std::vector<zklaim_ctx *> ptrs;
+    for (size_t i = 0; i < count; i++) {
+        creds.emplace_back(new Credential(b->payloads, seed0 + i));
+        zklaim_ctx &c = creds.back()->ctx;
+        c.pk_size = b->issuer->ctx.pk_size;
+        c.pk = (unsigned char *)malloc(c.pk_size);
+        memcpy(c.pk, b->issuer->ctx.pk, c.pk_size);
+        c.vk_size = b->issuer->ctx.vk_size;
+        c.vk = (unsigned char *)malloc(c.vk_size);
+        memcpy(c.vk, b->issuer->ctx.vk, c.vk_size);
+        ptrs.push_back(&c);
+    }
+    if ((count == 1 ? zkb_libsnark_prove(ptrs[0]) : zkb_libsnark_prove_batch(ptrs.data(), count)) != 0) return -1;
+    if (tamper < count && count > 1) {
+        const size_t other = (tamper + 1) % count;
+        memcpy(ptrs[tamper]->proof, ptrs[other]->proof, ptrs[other]->proof_size);
+    }
+    std::vector<int> ref_res(count), gpu_res(count, -7);
+    double t = now_s();
+    for (size_t i = 0; i < count; i++) ref_res[i] = libsnark_verify(ptrs[i]);
+    seconds[0] = now_s() - t;
+    t = now_s();
+    if (zkb_libsnark_verify_batch(ptrs.data(), count, gpu_res.data()) != 0) return -2;
+    seconds[1] = now_s() - t;
+    int agree = 0;
+    *accepted = 0;
+    for (size_t i = 0; i < count; i++) {
+        agree += ref_res[i] == gpu_res[i] ? 1 : 0;
+        *accepted += gpu_res[i] == 0 ? 1 : 0;
+    }
+    return agree;
 }
 
 /* A `payloads`-payload credential end to end on a GPU-made key: zkb_libsnark_trusted_setup, then a proof by the

@@ -58,3 +58,15 @@ def test_trusted_setup_on_the_gpu_gives_a_key_the_reference_accepts(cred, stock_
     from zklaim_b200 import bridge
     rc, t_setup, t_prove, t_verify = bridge.setup_roundtrip(1, seed=11, stock_prover=stock_prover)
     assert rc == 0
+
+
+def test_batch_verification_through_the_zklaim_entry_point(cred):
+    """zkb_libsnark_verify_batch (keys / proofs parsed by the reference's importers, zklaim_input_map for the public
+    input, pairings on the GPU) returns what the reference's libsnark_verify returns, credential by credential --
+    including one that carries another credential's proof."""
+    agree, accepted, t_ref, t_gpu = cred.verify_roundtrip(16, seed0=9000, tamper=3)
+    assert agree == 16
+    assert accepted == 15
+    agree, accepted, _, _ = cred.verify_roundtrip(1, seed0=9100)
+    assert (agree, accepted) == (1, 1)
+    print(f"\nverify 16 credentials: reference libsnark_verify {t_ref * 1e3:.1f} ms, zkb_libsnark_verify_batch {t_gpu * 1e3:.1f} ms")

@@ -28,6 +28,7 @@ _SIG = {
     "zkbr_witnesses": (_i, [_vp, _sz, _u64, _vp]),
     "zkbr_random_fr": (None, [_sz, _vp]),
     "zkbr_verify": (_i, [_vp, _vp, _vp]),
+    "zkbr_verify_roundtrip": (_i, [_vp, _sz, _u64, _sz, C.POINTER(_i), C.POINTER(C.c_double)]),
     "zkbr_roundtrip": (_i, [_vp, _sz, _u64, _vp]),
     "zkbr_prove_tampered": (_i, [_vp, _u64]),
     "zkbr_setup_roundtrip": (_i, [_sz, _u64, _i, _vp]),
@@ -94,6 +95,15 @@ class Credentials:
         t = (C.c_double * 2)()
         ok = self.L.zkbr_roundtrip(self.h, count, seed0, t)
         return ok, t[0], t[1]
+
+    def verify_roundtrip(self, count: int, seed0: int = 9000, tamper: int = -1):
+        """count credentials proved by zkb_libsnark_prove_batch, then verified by the reference's libsnark_verify AND by
+        zkb_libsnark_verify_batch (GPU); credential `tamper` carries its neighbour's proof.
+        Returns (credentials on which both verifiers agree, accepted by the GPU verifier, reference s, GPU s)."""
+        t = (C.c_double * 2)()
+        acc = C.c_int(0)
+        agree = self.L.zkbr_verify_roundtrip(self.h, count, seed0, tamper if tamper >= 0 else count, C.byref(acc), t)
+        return agree, acc.value, t[0], t[1]
 
     def prove_tampered(self, seed: int = 77) -> int:
         """zkb_libsnark_prove on a credential whose hash was tampered with: the reference's contract says 1"""
