@@ -1,7 +1,7 @@
 // CPU build of zklaim_b200/csrc/pairing.cuh's portable path: lets the (GPU-less) test-suite check the
 // tower arithmetic, the Miller loop and the final exponentiation against libff (oracle/_ref) before
 // the same source runs as device code.
-#include "../../zklaim_b200/csrc/pairing.cuh"
+#include "../../zklaim_b200/csrc/pairing_coop.cuh"
 #include <cstring>
 using namespace zkb;
 
@@ -86,4 +86,19 @@ extern "C" int hostpair_verify(const uint32_t *alpha_beta, const uint32_t *gamma
     const bool eq = groth16_pairing_check(miller_loop(ax, ay, bx, by, K), miller_loop(accx, accy, g.x, g.y, K),
                                           miller_loop(cx, cy, d.x, d.y, K), ab, K);
     return wf && eq;
+}
+
+// the six-lane cooperative form (pairing_coop.cuh), lanes emulated by a loop per phase
+extern "C" void hostpair_pairing_coop(const uint32_t *p, const uint32_t *q, int reduced, uint32_t *out)
+{
+    Fq px, py;
+    Fq2 qx, qy;
+    memcpy(&px, p, 32);
+    memcpy(&py, p + 8, 32);
+    memcpy(&qx, q, 64);
+    memcpy(&qy, q + 16, 64);
+    static Fq2 S[COOP_FE_REGS > COOP_MILLER_REGS ? COOP_FE_REGS : COOP_MILLER_REGS];
+    coop_miller_loop(S, px, py, qx, qy, consts());
+    if (reduced) coop_final_exponentiation(S, consts());
+    memcpy(out, S, 6 * sizeof(Fq2));
 }

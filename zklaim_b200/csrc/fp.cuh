@@ -364,7 +364,11 @@ template <class PR> struct Fp {
     // Translation units that are latency- rather than throughput-bound define ZKB_NOINLINE_MUL:
     // the ~300-instruction product then becomes one function per field instead of being
     // expanded at every use (ptxas time drops by an order of magnitude).
-    static ZKB_MUL_ATTR Fp mont_mul(const Fp &a, const Fp &b)
+    static ZKB_MUL_ATTR Fp mont_mul(const Fp &a, const Fp &b) { return mont_mul_inline(a, b); }
+    // The product itself, always expanded in place: for callers that put several INDEPENDENT products into one basic
+    // block (an Fq2 product is three) so that ptxas interleaves their carry chains -- a lone warp per scheduler
+    // otherwise waits out every dependent IMAD.
+    static ZKB_HD Fp mont_mul_inline(const Fp &a, const Fp &b)
     {
         uint32_t x[8], y[8];
         row_first(x, y, a.v, b.v[0]);

@@ -35,9 +35,25 @@ ZKB_HD Fq2 mul_xi(const Fq2 &a)
     return Fq2{a8.c0 + a.c0 - a.c1, a8.c1 + a.c1 + a.c0};
 }
 ZKB_HD Fq2 conj(const Fq2 &a) { return Fq2{a.c0, a.c1.neg()}; }
-ZKB_HD Fq2 mul_fq(const Fq2 &a, const Fq &k) { return Fq2{a.c0 * k, a.c1 * k}; }
-ZKB_NI Fq2 mul2(const Fq2 &a, const Fq2 &b) { return a * b; }
-ZKB_NI Fq2 sqr2(const Fq2 &a) { return a.sqr(); }
+// The Fq2 products of this file expand their two or three independent base-field products in ONE basic block
+// (Fq::mont_mul_inline), so the instruction scheduler interleaves the carry chains: the kernels built from them
+// run one warp per scheduler and are bound by dependent-issue latency, not by throughput.
+ZKB_NI Fq2 mul_fq(const Fq2 &a, const Fq &k) { return Fq2{Fq::mont_mul_inline(a.c0, k), Fq::mont_mul_inline(a.c1, k)}; }
+ZKB_NI Fq2 mul2(const Fq2 &a, const Fq2 &b)
+{
+    const Fq s0 = a.c0 + a.c1, s1 = b.c0 + b.c1;
+    const Fq aa = Fq::mont_mul_inline(a.c0, b.c0);
+    const Fq bb = Fq::mont_mul_inline(a.c1, b.c1);
+    const Fq s = Fq::mont_mul_inline(s0, s1);
+    return Fq2{aa - bb, s - aa - bb};
+}
+ZKB_NI Fq2 sqr2(const Fq2 &a)
+{
+    const Fq s = a.c0 + a.c1, d = a.c0 - a.c1;
+    const Fq ab = Fq::mont_mul_inline(a.c0, a.c1);
+    const Fq t = Fq::mont_mul_inline(s, d);
+    return Fq2{t, ab.dbl()};
+}
 
 struct Fq6 {
     Fq2 c0, c1, c2;

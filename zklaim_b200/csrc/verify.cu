@@ -15,9 +15,10 @@
 // Latency-bound (dependent 254-bit products): built with the out-of-line multiplier.
 #define ZKB_NOINLINE_MUL 1
 #include "common.cuh"
-#include "pairing.cuh"
+#include "pairing_coop.cuh"
 
 #include <mutex>
+#include <stdlib.h>
 
 using namespace zkb;
 
@@ -115,6 +116,106 @@ __global__ void k_pairing(const G1Affine *P, const G2Affine *Q, const PairingCon
     st_vec(out + i, f);
 }
 
+// ---- six lanes per Miller loop / final exponentiation (pairing_coop.cuh) ---------------------------------------
+constexpr int GROUPS = 32 / COOP_GROUP; // groups per block (one warp)
+
+// group t = which * n + i as in k_vf_miller; lanes 0 and 1 prepare the affine G1 / G2 inputs, then the group runs
+// the loop together
+__global__ void __launch_bounds__(32) k_vf_miller_coop(const ProofJ *proofs, const G1X *T, const G1Affine *gamma_abc,
+                                                       const G2Affine *gamma_g2, const G2Affine *delta_g2, const PairingConsts *Kp,
+                                                       Fq12 *F, uint32_t *wf, uint32_t n, uint32_t ni)
+{
+    __shared__ Fq2 S[GROUPS][COOP_MILLER_REGS];
+    __shared__ Fq2 Qin[GROUPS][2];
+    __shared__ Fq Pin[GROUPS][2];
+    __shared__ uint32_t ok_bits[GROUPS][2];
+    const int grp = threadIdx.x / COOP_GROUP, lane = threadIdx.x % COOP_GROUP;
+    uint32_t t = blockIdx.x * GROUPS + grp;
+    const bool live = t < 3 * n;
+    if (!live) t = 3 * n - 1; // a whole warp walks the same phases: spare groups redo the last unit and drop the result
+    const uint32_t which = t / n, i = t % n;
+    const PairingConsts &K = *Kp;
+    if (lane == 0) { // the G1 side
+        Fq three = Fq::one();
+        three = three + three.dbl();
+        bool ok = true;
+        if (which == 1) {
+            G1X acc = G1X::from_affine(ld_vec(gamma_abc));
+            for (uint32_t j = 0; j < ni; j++) acc.add(ld_vec(T + (size_t)i * ni + j));
+            jac_to_affine<Fq>(acc.to_jacobian(), Pin[grp][0], Pin[grp][1]);
+        } else {
+            const G1J A = ld_vec(which == 0 ? &proofs[i].A : &proofs[i].C);
+            ok = jacobian_well_formed<Fq>(A.X, A.Y, A.Z, three);
+            jac_to_affine<Fq>(A, Pin[grp][0], Pin[grp][1]);
+        }
+        ok_bits[grp][0] = ok;
+    }
+    if (lane == 1) { // the G2 side
+        bool ok = true;
+        if (which == 0) {
+            const G2J B = ld_vec(&proofs[i].B);
+            ok = jacobian_well_formed<Fq2>(B.X, B.Y, B.Z, K.twist_b);
+            jac_to_affine<Fq2>(B, Qin[grp][0], Qin[grp][1]);
+        } else {
+            affine_in<Fq2>(ld_vec(which == 1 ? gamma_g2 : delta_g2), Qin[grp][0], Qin[grp][1]);
+        }
+        ok_bits[grp][1] = ok;
+    }
+    __syncwarp();
+    const Fq px = Pin[grp][0], py = Pin[grp][1];
+    const Fq2 qx = Qin[grp][0], qy = Qin[grp][1];
+    coop_miller_loop(S[grp], px, py, qx, qy, K);
+    if (live && lane < COOP_LANES) st_vec((Fq2 *)(F + t) + lane, S[grp][lane]);
+    if (live && lane == 0) wf[t] = ok_bits[grp][0] & ok_bits[grp][1];
+}
+
+// group i: the decision for proof i
+__global__ void __launch_bounds__(32) k_vf_final_coop(const Fq12 *F, const uint32_t *wf, const Fq12 *alpha_beta, const PairingConsts *Kp,
+                                                      int32_t *accept, uint32_t n)
+{
+    __shared__ Fq2 S[GROUPS][COOP_FE_REGS];
+    const int grp = threadIdx.x / COOP_GROUP, lane = threadIdx.x % COOP_GROUP;
+    uint32_t i = blockIdx.x * GROUPS + grp;
+    const bool live = i < n;
+    if (!live) i = n - 1;
+    Fq2 *s = S[grp];
+    // s[0..5] = ML(A, B) * conj(ML(acc, gamma) * ML(C, delta))
+    if (lane < COOP_LANES) {
+        s[6 + lane] = ld_vec((const Fq2 *)(F + n + i) + lane);
+        s[12 + lane] = ld_vec((const Fq2 *)(F + 2 * n + i) + lane);
+        s[lane] = ld_vec((const Fq2 *)(F + i) + lane);
+    }
+    __syncwarp();
+    coop_mul12(s + 6, s + 6, s + 12, s + 60);
+    coop_conj12(s + 6, s + 6);
+    coop_mul12(s, s, s + 6, s + 60);
+    coop_final_exponentiation(s, *Kp);
+    if (live && lane == 0) {
+        bool eq = true;
+        const Fq2 *ab = (const Fq2 *)alpha_beta;
+        for (int k = 0; k < 6; k++) eq = eq && s[k] == ld_vec(ab + k);
+        accept[i] = (wf[i] && wf[2 * n + i] && eq) ? 1 : 0;
+    }
+}
+
+// group i: alt_bn128_ate_miller_loop / alt_bn128_reduced_pairing of one affine pair
+__global__ void __launch_bounds__(32) k_pairing_coop(const G1Affine *P, const G2Affine *Q, const PairingConsts *Kp, int reduced, Fq12 *out,
+                                                     uint32_t n)
+{
+    __shared__ Fq2 S[GROUPS][COOP_FE_REGS];
+    const int grp = threadIdx.x / COOP_GROUP, lane = threadIdx.x % COOP_GROUP;
+    uint32_t i = blockIdx.x * GROUPS + grp;
+    const bool live = i < n;
+    if (!live) i = n - 1;
+    Fq px, py;
+    Fq2 qx, qy;
+    affine_in<Fq>(ld_vec(P + i), px, py);
+    affine_in<Fq2>(ld_vec(Q + i), qx, qy);
+    coop_miller_loop(S[grp], px, py, qx, qy, *Kp);
+    if (reduced) coop_final_exponentiation(S[grp], *Kp);
+    if (live && lane < COOP_LANES) st_vec((Fq2 *)(out + i) + lane, S[grp][lane]);
+}
+
 const PairingConsts &host_consts()
 {
     static PairingConsts K;
@@ -136,6 +237,16 @@ int consts_on_device(zkb_ctx *ctx, const PairingConsts **out)
 }
 
 constexpr int LANES = 32; // one warp per block: the lanes of a warp run identical instruction streams
+constexpr size_t COOP_MAX_BATCH = 1024; // above this the one-lane kernels have filled the device anyway
+// ZKB_VERIFY_COOP=0 selects the one-lane kernels at every size (measurement switch)
+bool coop_enabled()
+{
+    static const bool on = [] {
+        const char *e = getenv("ZKB_VERIFY_COOP");
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
 } // namespace
 
 extern "C" {
@@ -157,7 +268,10 @@ int zkb_pairing(zkb_ctx *ctx, const uint64_t *g1_affine, const uint64_t *g2_affi
     ZKB_CUDA(ctx, cudaMemcpyAsync(dQ, g2_affine, n * sizeof(G2Affine), cudaMemcpyHostToDevice, ctx->stream));
     ZKB_CUDA(ctx, cudaMemcpyAsync(dP, g1_affine, n * sizeof(G1Affine), cudaMemcpyHostToDevice, ctx->stream));
     ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    k_pairing<<<ceil_div(n, LANES), LANES, 0, ctx->stream>>>(dP, dQ, K, reduced, ctx->scratch[SV_F].as<Fq12>(), (uint32_t)n);
+    if (coop_enabled())
+        k_pairing_coop<<<ceil_div(n, GROUPS), 32, 0, ctx->stream>>>(dP, dQ, K, reduced, ctx->scratch[SV_F].as<Fq12>(), (uint32_t)n);
+    else
+        k_pairing<<<ceil_div(n, LANES), LANES, 0, ctx->stream>>>(dP, dQ, K, reduced, ctx->scratch[SV_F].as<Fq12>(), (uint32_t)n);
     ZKB_LAUNCH_CHECK(ctx);
     ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, ctx->scratch[SV_F].p, n * sizeof(Fq12), cudaMemcpyDeviceToHost, ctx->stream));
@@ -209,11 +323,21 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
         k_vf_inputs<<<ceil_div((size_t)nn * ni, LANES), LANES, 0, st>>>((const Fr *)(base + o_in), d_abc, dT, nn, ni);
         ZKB_LAUNCH_CHECK(ctx);
     }
-    k_vf_miller<<<ceil_div(3 * n, LANES), LANES, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
-                                                        (const G2Affine *)(base + o_d), K, dF, d_wf, nn, ni);
-    ZKB_LAUNCH_CHECK(ctx);
-    k_vf_final<<<ceil_div(n, LANES), LANES, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
-    ZKB_LAUNCH_CHECK(ctx);
+    // small batches: six lanes per Miller loop / final exponentiation (the device is empty, latency is what counts);
+    // large batches: one lane each (fewer instructions in total once every warp slot is busy)
+    if (coop_enabled() && n <= COOP_MAX_BATCH) {
+        k_vf_miller_coop<<<ceil_div(3 * n, GROUPS), 32, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
+                                                                (const G2Affine *)(base + o_d), K, dF, d_wf, nn, ni);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_vf_final_coop<<<ceil_div(n, GROUPS), 32, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
+        ZKB_LAUNCH_CHECK(ctx);
+    } else {
+        k_vf_miller<<<ceil_div(3 * n, LANES), LANES, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
+                                                            (const G2Affine *)(base + o_d), K, dF, d_wf, nn, ni);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_vf_final<<<ceil_div(n, LANES), LANES, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
+        ZKB_LAUNCH_CHECK(ctx);
+    }
     ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
     ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_acc, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     ZKB_CUDA(ctx, cudaStreamSynchronize(st));
