@@ -76,3 +76,27 @@ def test_zklaim_batch_prove_then_verify_on_gpu(zctx, ref):
     print(f"\nverify_batch: {n} proofs, {ni} public inputs: {zctx.last_device_ms():.2f} ms device, {wall * 1e3:.2f} ms wall")
     key.free()
     circ.free()
+
+
+def test_key_table_cache_follows_the_verification_key(zctx, ref):
+    """zkb_verify_batch keeps the window table of gamma_ABC_g1 while the key stays the same: alternate two keys with
+    the same number of inputs and check every call's decisions (a stale table would reject the valid proofs)."""
+    g = np.load(os.path.join(GOLD, "verify.npz"))
+    vk1 = {k: g[k] for k in ("alpha_g1_beta_g2", "gamma_g2", "delta_g2", "gamma_ABC_g1")}
+    ni = len(vk1["gamma_ABC_g1"]) - 1
+    circ = ref.Circuit.example(41, ni, seed=41)
+    circ.setup()
+    w = circ.witness()
+    pr2 = np.stack([circ.prove(w, ref.sha512_rng(70 + k, 1)[0], ref.sha512_rng(80 + k, 1)[0], want_H=False)["proof"]
+                    for k in range(3)]).reshape(3, 48)
+    vk2 = circ.export_vk()
+    vk2["alpha_g1_beta_g2"] = circ.vk_alpha_beta()
+    x2 = np.tile(w[:ni], (3, 1, 1))
+    exp1 = g["accept"].astype(bool).tolist()
+    for _ in range(2):
+        assert zctx.verify_batch(vk1, g["primary"], g["proofs"]).tolist() == exp1
+        assert zctx.verify_batch(vk1, g["primary"], g["proofs"]).tolist() == exp1  # table reused
+        assert zctx.verify_batch(vk2, x2, pr2).tolist() == [True, True, True]
+        # proofs of key 2 under key 1: rejected
+        assert zctx.verify_batch(vk1, x2, pr2).tolist() == [False, False, False]
+    circ.free()

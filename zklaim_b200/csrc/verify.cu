@@ -23,7 +23,7 @@
 using namespace zkb;
 
 namespace {
-enum { SV_CONST = 58, SV_IN, SV_T, SV_F, SV_OUT }; // scratch slots of this file (prover.cu ends at 57)
+enum { SV_CONST = 58, SV_IN, SV_T, SV_F, SV_OUT, SV_TAB }; // scratch slots of this file (prover.cu ends at 57)
 
 // affine limbs at the ABI: all-zero = infinity (zkb.h conventions)
 template <class F> __device__ void affine_in(const Affine<F> &a, F &x, F &y)
@@ -47,6 +47,37 @@ __global__ void k_vf_inputs(const Fr *primary, const G1Affine *gamma_abc, G1X *T
     const uint32_t j = t % ni;
     const Fr k = ld_vec(primary + t).from_mont();
     st_vec(T + t, scalar_mul<Fq>(k.v, G1X::from_affine(ld_vec(gamma_abc + j + 1))));
+}
+
+// Public-input sums with a per-key table: input_j * P_j = sum_c chunk_c * (2^(32 c) P_j), eight 32-bit chunks.
+// The 8 multiples of every gamma_ABC[j + 1] are made once per verification key (k_vf_tab; zkb_verify_batch keeps them
+// while the key stays the same), after which a lane's chain is 32 doublings instead of 254.
+constexpr uint32_t VF_CHUNKS = 8;
+__global__ void k_vf_tab(const G1Affine *gamma_abc, G1Affine *tab, uint32_t ni)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ni * VF_CHUNKS) return;
+    const uint32_t j = t / VF_CHUNKS, c = t % VF_CHUNKS;
+    G1X p = G1X::from_affine(ld_vec(gamma_abc + j + 1));
+    for (uint32_t k = 0; k < 32 * c; k++) p = p.dbl();
+    G1Affine a;
+    if (p.is_inf()) {
+        a.x = Fq::zero();
+        a.y = Fq::zero();
+    } else {
+        jac_to_affine<Fq>(p.to_jacobian(), a.x, a.y);
+    }
+    st_vec(tab + t, a);
+}
+// lane t = (proof i, input j, chunk c): T[t] = chunk_c(input_ij) * tab[j][c]
+__global__ void k_vf_inputs_tab(const Fr *primary, const G1Affine *tab, G1X *T, uint32_t n, uint32_t ni)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * ni * VF_CHUNKS) return;
+    const uint32_t c = t % VF_CHUNKS, ij = t / VF_CHUNKS, j = ij % ni;
+    const Fr k = ld_vec(primary + ij).from_mont();
+    uint32_t kc[8] = {k.v[c], 0, 0, 0, 0, 0, 0, 0};
+    st_vec(T + t, scalar_mul<Fq>(kc, G1X::from_affine(ld_vec(tab + j * VF_CHUNKS + c))));
 }
 
 struct ProofJ { // zkb_proof_out layout
@@ -123,9 +154,10 @@ constexpr int GROUPS = 32 / COOP_GROUP; // groups per block (one warp)
 // the loop together
 __global__ void __launch_bounds__(32) k_vf_miller_coop(const ProofJ *proofs, const G1X *T, const G1Affine *gamma_abc,
                                                        const G2Affine *gamma_g2, const G2Affine *delta_g2, const PairingConsts *Kp,
-                                                       Fq12 *F, uint32_t *wf, uint32_t n, uint32_t ni)
+                                                       Fq12 *F, uint32_t *wf, uint32_t n, uint32_t nt /* terms of acc per proof */)
 {
     __shared__ Fq2 S[GROUPS][COOP_MILLER_REGS];
+    __shared__ G1X part[GROUPS][COOP_LANES];
     __shared__ Fq2 Qin[GROUPS][2];
     __shared__ Fq Pin[GROUPS][2];
     __shared__ uint32_t ok_bits[GROUPS][2];
@@ -135,13 +167,19 @@ __global__ void __launch_bounds__(32) k_vf_miller_coop(const ProofJ *proofs, con
     if (!live) t = 3 * n - 1; // a whole warp walks the same phases: spare groups redo the last unit and drop the result
     const uint32_t which = t / n, i = t % n;
     const PairingConsts &K = *Kp;
+    if (which == 1 && lane < COOP_LANES) { // the nt terms of acc, strided over the lanes
+        G1X s = G1X::inf();
+        for (uint32_t k = lane; k < nt; k += COOP_LANES) s.add(ld_vec(T + (size_t)i * nt + k));
+        part[grp][lane] = s;
+    }
+    __syncwarp();
     if (lane == 0) { // the G1 side
         Fq three = Fq::one();
         three = three + three.dbl();
         bool ok = true;
         if (which == 1) {
             G1X acc = G1X::from_affine(ld_vec(gamma_abc));
-            for (uint32_t j = 0; j < ni; j++) acc.add(ld_vec(T + (size_t)i * ni + j));
+            for (int k = 0; k < COOP_LANES; k++) acc.add(part[grp][k]);
             jac_to_affine<Fq>(acc.to_jacobian(), Pin[grp][0], Pin[grp][1]);
         } else {
             const G1J A = ld_vec(which == 0 ? &proofs[i].A : &proofs[i].C);
@@ -301,7 +339,7 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
     const size_t total = o_in + n * (size_t)ni * sizeof(Fr);
     static_assert(sizeof(ProofJ) == 48 * 8, "zkb_proof_out layout");
     ZKB_CUDA(ctx, ctx->scratch[SV_IN].ensure(total));
-    ZKB_CUDA(ctx, ctx->scratch[SV_T].ensure((size_t)nn * (ni ? ni : 1) * sizeof(G1X)));
+    ZKB_CUDA(ctx, ctx->scratch[SV_T].ensure((size_t)nn * (ni ? ni : 1) * VF_CHUNKS * sizeof(G1X)));
     ZKB_CUDA(ctx, ctx->scratch[SV_F].ensure(3 * n * sizeof(Fq12)));
     ZKB_CUDA(ctx, ctx->scratch[SV_OUT].ensure(4 * n * sizeof(uint32_t)));
     if (ensure_pinned(ctx, n * sizeof(int32_t))) return ZKB_ERR_CUDA;
@@ -319,15 +357,32 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
     Fq12 *dF = ctx->scratch[SV_F].as<Fq12>();
     uint32_t *d_wf = ctx->scratch[SV_OUT].as<uint32_t>();
     int32_t *d_acc = (int32_t *)(d_wf + 3 * n);
-    if (ni) {
+    const bool coop = coop_enabled() && n <= COOP_MAX_BATCH;
+    uint32_t nt = ni; // terms of acc per proof
+    if (ni && coop) {
+        // window table of the key: rebuilt only when gamma_ABC_g1 changes
+        const size_t abc_words = (size_t)(ni + 1) * 8;
+        const bool same = ctx->vf_abc_host.size() == abc_words && !memcmp(ctx->vf_abc_host.data(), vk->gamma_ABC_g1, abc_words * 8);
+        ZKB_CUDA(ctx, ctx->scratch[SV_TAB].ensure((size_t)ni * VF_CHUNKS * sizeof(G1Affine)));
+        G1Affine *d_tab = ctx->scratch[SV_TAB].as<G1Affine>();
+        if (!same) {
+            ctx->vf_abc_host.clear();
+            k_vf_tab<<<ceil_div((size_t)ni * VF_CHUNKS, LANES), LANES, 0, st>>>(d_abc, d_tab, ni);
+            ZKB_LAUNCH_CHECK(ctx);
+        }
+        nt = ni * VF_CHUNKS;
+        k_vf_inputs_tab<<<ceil_div((size_t)nn * nt, LANES), LANES, 0, st>>>((const Fr *)(base + o_in), d_tab, dT, nn, ni);
+        ZKB_LAUNCH_CHECK(ctx);
+        if (!same) ctx->vf_abc_host.assign(vk->gamma_ABC_g1, vk->gamma_ABC_g1 + abc_words);
+    } else if (ni) {
         k_vf_inputs<<<ceil_div((size_t)nn * ni, LANES), LANES, 0, st>>>((const Fr *)(base + o_in), d_abc, dT, nn, ni);
         ZKB_LAUNCH_CHECK(ctx);
     }
     // small batches: six lanes per Miller loop / final exponentiation (the device is empty, latency is what counts);
     // large batches: one lane each (fewer instructions in total once every warp slot is busy)
-    if (coop_enabled() && n <= COOP_MAX_BATCH) {
+    if (coop) {
         k_vf_miller_coop<<<ceil_div(3 * n, GROUPS), 32, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
-                                                                (const G2Affine *)(base + o_d), K, dF, d_wf, nn, ni);
+                                                                (const G2Affine *)(base + o_d), K, dF, d_wf, nn, nt);
         ZKB_LAUNCH_CHECK(ctx);
         k_vf_final_coop<<<ceil_div(n, GROUPS), 32, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
         ZKB_LAUNCH_CHECK(ctx);
