@@ -86,6 +86,13 @@ inline G2T get_g2_jacobian(const uint64_t *src)
                libff::alt_bn128_Fq2(get_fp(src + 16), get_fp(src + 20)));
 }
 
+inline libff::alt_bn128_Fq2 get_fp2(const uint64_t *src) { return libff::alt_bn128_Fq2(get_fp(src), get_fp(src + 4)); }
+inline libff::alt_bn128_Fq12 get_fq12(const uint64_t *src) /* 48 limbs, member order c0.c0.c0 .. c1.c2.c1 */
+{
+    return libff::alt_bn128_Fq12(libff::alt_bn128_Fq6(get_fp2(src), get_fp2(src + 8), get_fp2(src + 16)),
+                                 libff::alt_bn128_Fq6(get_fp2(src + 24), get_fp2(src + 32), get_fp2(src + 40)));
+}
+
 /* flat copy of a proving key; owns the storage the zkb_key_desc points into */
 struct KeyArrays {
     std::vector<uint64_t> row_ptr[3], coeff[3];
@@ -489,8 +496,11 @@ inline libsnark::r1cs_gg_ppzksnark_keypair<PP> generator_with_randomness(const l
     G2T beta_g2 = get_g2_affine(o.beta_g2), delta_g2 = get_g2_affine(o.delta_g2), gamma_g2 = get_g2_affine(o.gamma_g2);
     G1T abc0 = get_g1_affine(&abc[0]);
     libsnark::accumulation_vector<G1T> gamma_ABC_g1(std::move(abc0), std::move(abc_rest));
-    /* the one pairing of the verification key stays libff's (r1cs_gg_ppzksnark.tcc:338) */
-    libsnark::r1cs_gg_ppzksnark_verification_key<PP> vk(PP::reduced_pairing(alpha_g1, beta_g2), gamma_g2, delta_g2, gamma_ABC_g1);
+    /* the one pairing of the verification key (r1cs_gg_ppzksnark.tcc:338): zkb_pairing, bit-identical to reduced_pairing */
+    uint64_t ab[48];
+    if (zkb_pairing(ctx, o.alpha_g1, o.beta_g2, 1, 1, ab) != ZKB_OK)
+        throw std::runtime_error(std::string("zkb_pairing failed: ") + zkb_last_error(ctx));
+    libsnark::r1cs_gg_ppzksnark_verification_key<PP> vk(get_fq12(ab), gamma_g2, delta_g2, gamma_ABC_g1);
     G2T delta_g2_pk = delta_g2;
     libsnark::r1cs_gg_ppzksnark_proving_key<PP> pk(std::move(alpha_g1), std::move(beta_g1), std::move(beta_g2), std::move(delta_g1),
                                                    std::move(delta_g2_pk), std::move(Aq), std::move(Bq), std::move(Hq), std::move(Lq),
