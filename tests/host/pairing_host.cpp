@@ -88,8 +88,15 @@ extern "C" int hostpair_verify(const uint32_t *alpha_beta, const uint32_t *gamma
     return wf && eq;
 }
 
-// the six-lane cooperative form (pairing_coop.cuh), lanes emulated by a loop per phase
-extern "C" void hostpair_pairing_coop(const uint32_t *p, const uint32_t *q, int reduced, uint32_t *out)
+// the cooperative forms (pairing_coop.cuh: 6 or 18 lanes per pairing), lanes emulated by a loop per phase
+template <int NL> static void pairing_coop(const Fq &px, const Fq &py, const Fq2 &qx, const Fq2 &qy, int reduced, uint32_t *out)
+{
+    static Fq2 S[COOP_FE_REGS > COOP_MILLER_REGS ? COOP_FE_REGS : COOP_MILLER_REGS];
+    coop_miller_loop<NL>(S, px, py, qx, qy, consts());
+    if (reduced) coop_final_exponentiation<NL>(S, consts());
+    memcpy(out, S, 6 * sizeof(Fq2));
+}
+extern "C" void hostpair_pairing_coop(const uint32_t *p, const uint32_t *q, int reduced, int lanes, uint32_t *out)
 {
     Fq px, py;
     Fq2 qx, qy;
@@ -97,8 +104,8 @@ extern "C" void hostpair_pairing_coop(const uint32_t *p, const uint32_t *q, int 
     memcpy(&py, p + 8, 32);
     memcpy(&qx, q, 64);
     memcpy(&qy, q + 16, 64);
-    static Fq2 S[COOP_FE_REGS > COOP_MILLER_REGS ? COOP_FE_REGS : COOP_MILLER_REGS];
-    coop_miller_loop(S, px, py, qx, qy, consts());
-    if (reduced) coop_final_exponentiation(S, consts());
-    memcpy(out, S, 6 * sizeof(Fq2));
+    if (lanes == 18)
+        pairing_coop<18>(px, py, qx, qy, reduced, out);
+    else
+        pairing_coop<6>(px, py, qx, qy, reduced, out);
 }

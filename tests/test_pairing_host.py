@@ -46,9 +46,10 @@ def test_pairing_matches_reference(host, reduced):
         assert np.array_equal(out, exp[i]), i
 
 
+@pytest.mark.parametrize("lanes", [6, 18])
 @pytest.mark.parametrize("reduced", [0, 1])
-def test_cooperative_lane_program_matches_reference(host, reduced):
-    """pairing_coop.cuh (six lanes per pairing; on the host the lanes of a phase run one after the other) gives the
+def test_cooperative_lane_program_matches_reference(host, reduced, lanes):
+    """pairing_coop.cuh (6 or 18 lanes per pairing; on the host the lanes of a phase run one after the other) gives the
     reference's Miller-loop and reduced-pairing values"""
     g = np.load(os.path.join(GOLD, "pairing.npz"))
     exp = g["reduced" if reduced else "miller"]
@@ -58,7 +59,7 @@ def test_cooperative_lane_program_matches_reference(host, reduced):
             p = p.copy()
             p[4:] = np.array([0xd35d438dc58f0d9d, 0x0a78eb28f5c70b3d, 0x666ea36f7879462c, 0x0e0a77c19a07df2f], dtype=np.uint64)
         out = np.zeros(48, dtype=np.uint64)
-        host.hostpair_pairing_coop(_p(p), _p(q), reduced, _p(out))
+        host.hostpair_pairing_coop(_p(p), _p(q), reduced, lanes, _p(out))
         assert np.array_equal(out, exp[i]), i
 
 

@@ -148,14 +148,14 @@ __global__ void k_pairing(const G1Affine *P, const G2Affine *Q, const PairingCon
 }
 
 // ---- six lanes per Miller loop / final exponentiation (pairing_coop.cuh) ---------------------------------------
-constexpr int GROUPS = 32 / COOP_GROUP; // groups per block (one warp)
 
 // group t = which * n + i as in k_vf_miller; lanes 0 and 1 prepare the affine G1 / G2 inputs, then the group runs
 // the loop together
-__global__ void __launch_bounds__(32) k_vf_miller_coop(const ProofJ *proofs, const G1X *T, const G1Affine *gamma_abc,
+template <int NL> __global__ void __launch_bounds__(32) k_vf_miller_coop(const ProofJ *proofs, const G1X *T, const G1Affine *gamma_abc,
                                                        const G2Affine *gamma_g2, const G2Affine *delta_g2, const PairingConsts *Kp,
                                                        Fq12 *F, uint32_t *wf, uint32_t n, uint32_t nt /* terms of acc per proof */)
 {
+    constexpr int COOP_GROUP = coop_group(NL), GROUPS = 32 / COOP_GROUP, COOP_LANES = 6;
     __shared__ Fq2 S[GROUPS][COOP_MILLER_REGS];
     __shared__ G1X part[GROUPS][COOP_LANES];
     __shared__ Fq2 Qin[GROUPS][2];
@@ -202,15 +202,16 @@ __global__ void __launch_bounds__(32) k_vf_miller_coop(const ProofJ *proofs, con
     __syncwarp();
     const Fq px = Pin[grp][0], py = Pin[grp][1];
     const Fq2 qx = Qin[grp][0], qy = Qin[grp][1];
-    coop_miller_loop(S[grp], px, py, qx, qy, K);
+    coop_miller_loop<NL>(S[grp], px, py, qx, qy, K);
     if (live && lane < COOP_LANES) st_vec((Fq2 *)(F + t) + lane, S[grp][lane]);
     if (live && lane == 0) wf[t] = ok_bits[grp][0] & ok_bits[grp][1];
 }
 
 // group i: the decision for proof i
-__global__ void __launch_bounds__(32) k_vf_final_coop(const Fq12 *F, const uint32_t *wf, const Fq12 *alpha_beta, const PairingConsts *Kp,
+template <int NL> __global__ void __launch_bounds__(32) k_vf_final_coop(const Fq12 *F, const uint32_t *wf, const Fq12 *alpha_beta, const PairingConsts *Kp,
                                                       int32_t *accept, uint32_t n)
 {
+    constexpr int COOP_GROUP = coop_group(NL), GROUPS = 32 / COOP_GROUP, COOP_LANES = 6;
     __shared__ Fq2 S[GROUPS][COOP_FE_REGS];
     const int grp = threadIdx.x / COOP_GROUP, lane = threadIdx.x % COOP_GROUP;
     uint32_t i = blockIdx.x * GROUPS + grp;
@@ -224,10 +225,10 @@ __global__ void __launch_bounds__(32) k_vf_final_coop(const Fq12 *F, const uint3
         s[lane] = ld_vec((const Fq2 *)(F + i) + lane);
     }
     __syncwarp();
-    coop_mul12(s + 6, s + 6, s + 12, s + 60);
-    coop_conj12(s + 6, s + 6);
-    coop_mul12(s, s, s + 6, s + 60);
-    coop_final_exponentiation(s, *Kp);
+    coop_mul12<NL>(s + 6, s + 6, s + 12, s + 60);
+    coop_conj12<NL>(s + 6, s + 6);
+    coop_mul12<NL>(s, s, s + 6, s + 60);
+    coop_final_exponentiation<NL>(s, *Kp);
     if (live && lane == 0) {
         bool eq = true;
         const Fq2 *ab = (const Fq2 *)alpha_beta;
@@ -237,9 +238,10 @@ __global__ void __launch_bounds__(32) k_vf_final_coop(const Fq12 *F, const uint3
 }
 
 // group i: alt_bn128_ate_miller_loop / alt_bn128_reduced_pairing of one affine pair
-__global__ void __launch_bounds__(32) k_pairing_coop(const G1Affine *P, const G2Affine *Q, const PairingConsts *Kp, int reduced, Fq12 *out,
+template <int NL> __global__ void __launch_bounds__(32) k_pairing_coop(const G1Affine *P, const G2Affine *Q, const PairingConsts *Kp, int reduced, Fq12 *out,
                                                      uint32_t n)
 {
+    constexpr int COOP_GROUP = coop_group(NL), GROUPS = 32 / COOP_GROUP, COOP_LANES = 6;
     __shared__ Fq2 S[GROUPS][COOP_FE_REGS];
     const int grp = threadIdx.x / COOP_GROUP, lane = threadIdx.x % COOP_GROUP;
     uint32_t i = blockIdx.x * GROUPS + grp;
@@ -249,8 +251,8 @@ __global__ void __launch_bounds__(32) k_pairing_coop(const G1Affine *P, const G2
     Fq2 qx, qy;
     affine_in<Fq>(ld_vec(P + i), px, py);
     affine_in<Fq2>(ld_vec(Q + i), qx, qy);
-    coop_miller_loop(S[grp], px, py, qx, qy, *Kp);
-    if (reduced) coop_final_exponentiation(S[grp], *Kp);
+    coop_miller_loop<NL>(S[grp], px, py, qx, qy, *Kp);
+    if (reduced) coop_final_exponentiation<NL>(S[grp], *Kp);
     if (live && lane < COOP_LANES) st_vec((Fq2 *)(out + i) + lane, S[grp][lane]);
 }
 
@@ -275,15 +277,17 @@ int consts_on_device(zkb_ctx *ctx, const PairingConsts **out)
 }
 
 constexpr int LANES = 32; // one warp per block: the lanes of a warp run identical instruction streams
-constexpr size_t COOP_MAX_BATCH = 1024; // above this the one-lane kernels have filled the device anyway
-// ZKB_VERIFY_COOP=0 selects the one-lane kernels at every size (measurement switch)
-bool coop_enabled()
+// Lanes per pairing by batch size: 18 while a warp per pairing still leaves the device under-filled, 6 up to the size
+// where one lane per pairing has filled it anyway.  ZKB_VERIFY_COOP = 0 / 6 / 18 forces a form (measurement switch).
+int coop_lanes(size_t n)
 {
-    static const bool on = [] {
+    static const int forced = [] {
         const char *e = getenv("ZKB_VERIFY_COOP");
-        return !(e && e[0] == '0');
+        return e ? atoi(e) : -1;
     }();
-    return on;
+    if (forced == 0) return 1;
+    if (forced == 6 || forced == 18) return forced;
+    return n <= 128 ? 18 : (n <= 1024 ? 6 : 1);
 }
 } // namespace
 
@@ -306,8 +310,11 @@ int zkb_pairing(zkb_ctx *ctx, const uint64_t *g1_affine, const uint64_t *g2_affi
     ZKB_CUDA(ctx, cudaMemcpyAsync(dQ, g2_affine, n * sizeof(G2Affine), cudaMemcpyHostToDevice, ctx->stream));
     ZKB_CUDA(ctx, cudaMemcpyAsync(dP, g1_affine, n * sizeof(G1Affine), cudaMemcpyHostToDevice, ctx->stream));
     ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    if (coop_enabled())
-        k_pairing_coop<<<ceil_div(n, GROUPS), 32, 0, ctx->stream>>>(dP, dQ, K, reduced, ctx->scratch[SV_F].as<Fq12>(), (uint32_t)n);
+    const int lanes = coop_lanes(n);
+    if (lanes == 18)
+        k_pairing_coop<18><<<(unsigned)n, 32, 0, ctx->stream>>>(dP, dQ, K, reduced, ctx->scratch[SV_F].as<Fq12>(), (uint32_t)n);
+    else if (lanes == 6)
+        k_pairing_coop<6><<<ceil_div(n, 4), 32, 0, ctx->stream>>>(dP, dQ, K, reduced, ctx->scratch[SV_F].as<Fq12>(), (uint32_t)n);
     else
         k_pairing<<<ceil_div(n, LANES), LANES, 0, ctx->stream>>>(dP, dQ, K, reduced, ctx->scratch[SV_F].as<Fq12>(), (uint32_t)n);
     ZKB_LAUNCH_CHECK(ctx);
@@ -357,7 +364,8 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
     Fq12 *dF = ctx->scratch[SV_F].as<Fq12>();
     uint32_t *d_wf = ctx->scratch[SV_OUT].as<uint32_t>();
     int32_t *d_acc = (int32_t *)(d_wf + 3 * n);
-    const bool coop = coop_enabled() && n <= COOP_MAX_BATCH;
+    const int lanes = coop_lanes(n);
+    const bool coop = lanes > 1;
     uint32_t nt = ni; // terms of acc per proof
     if (ni && coop) {
         // window table of the key: rebuilt only when gamma_ABC_g1 changes
@@ -380,11 +388,17 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
     }
     // small batches: six lanes per Miller loop / final exponentiation (the device is empty, latency is what counts);
     // large batches: one lane each (fewer instructions in total once every warp slot is busy)
-    if (coop) {
-        k_vf_miller_coop<<<ceil_div(3 * n, GROUPS), 32, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
-                                                                (const G2Affine *)(base + o_d), K, dF, d_wf, nn, nt);
+    if (lanes == 18) {
+        k_vf_miller_coop<18><<<3 * nn, 32, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
+                                                   (const G2Affine *)(base + o_d), K, dF, d_wf, nn, nt);
         ZKB_LAUNCH_CHECK(ctx);
-        k_vf_final_coop<<<ceil_div(n, GROUPS), 32, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
+        k_vf_final_coop<18><<<nn, 32, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
+        ZKB_LAUNCH_CHECK(ctx);
+    } else if (lanes == 6) {
+        k_vf_miller_coop<6><<<ceil_div(3 * n, 4), 32, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
+                                                             (const G2Affine *)(base + o_d), K, dF, d_wf, nn, nt);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_vf_final_coop<6><<<ceil_div(n, 4), 32, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
         ZKB_LAUNCH_CHECK(ctx);
     } else {
         k_vf_miller<<<ceil_div(3 * n, LANES), LANES, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
