@@ -39,16 +39,6 @@ template <class F> __device__ void affine_in(const Affine<F> &a, F &x, F &y)
 
 __device__ Fq2 twist_b_of(const PairingConsts &K) { return K.twist_b; }
 
-// lane t = (proof i, input j): T = input_j * gamma_ABC[j + 1]
-__global__ void k_vf_inputs(const Fr *primary, const G1Affine *gamma_abc, G1X *T, uint32_t n, uint32_t ni)
-{
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n * ni) return;
-    const uint32_t j = t % ni;
-    const Fr k = ld_vec(primary + t).from_mont();
-    st_vec(T + t, scalar_mul<Fq>(k.v, G1X::from_affine(ld_vec(gamma_abc + j + 1))));
-}
-
 // Public-input sums with a per-key table: input_j * P_j = sum_c chunk_c * (2^(32 c) P_j), eight 32-bit chunks.
 // The 8 multiples of every gamma_ABC[j + 1] are made once per verification key (k_vf_tab; zkb_verify_batch keeps them
 // while the key stays the same), after which a lane's chain is 32 doublings instead of 254.
@@ -89,7 +79,8 @@ struct ProofJ { // zkb_proof_out layout
 // lane t = which * n + i: Miller loop `which` of proof i (0: (A, B), 1: (acc, gamma), 2: (C, delta)); also the
 // well-formedness bits of the points this lane touches
 __global__ void k_vf_miller(const ProofJ *proofs, const G1X *T, const G1Affine *gamma_abc, const G2Affine *gamma_g2,
-                            const G2Affine *delta_g2, const PairingConsts *Kp, Fq12 *F, uint32_t *wf, uint32_t n, uint32_t ni)
+                            const G2Affine *delta_g2, const PairingConsts *Kp, Fq12 *F, uint32_t *wf, uint32_t n,
+                            uint32_t ni /* terms of acc per proof */)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= 3 * n) return;
@@ -365,9 +356,8 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
     uint32_t *d_wf = ctx->scratch[SV_OUT].as<uint32_t>();
     int32_t *d_acc = (int32_t *)(d_wf + 3 * n);
     const int lanes = coop_lanes(n);
-    const bool coop = lanes > 1;
     uint32_t nt = ni; // terms of acc per proof
-    if (ni && coop) {
+    if (ni) {
         // window table of the key: rebuilt only when gamma_ABC_g1 changes
         const size_t abc_words = (size_t)(ni + 1) * 8;
         const bool same = ctx->vf_abc_host.size() == abc_words && !memcmp(ctx->vf_abc_host.data(), vk->gamma_ABC_g1, abc_words * 8);
@@ -382,9 +372,6 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
         k_vf_inputs_tab<<<ceil_div((size_t)nn * nt, LANES), LANES, 0, st>>>((const Fr *)(base + o_in), d_tab, dT, nn, ni);
         ZKB_LAUNCH_CHECK(ctx);
         if (!same) ctx->vf_abc_host.assign(vk->gamma_ABC_g1, vk->gamma_ABC_g1 + abc_words);
-    } else if (ni) {
-        k_vf_inputs<<<ceil_div((size_t)nn * ni, LANES), LANES, 0, st>>>((const Fr *)(base + o_in), d_abc, dT, nn, ni);
-        ZKB_LAUNCH_CHECK(ctx);
     }
     // small batches: six lanes per Miller loop / final exponentiation (the device is empty, latency is what counts);
     // large batches: one lane each (fewer instructions in total once every warp slot is busy)
@@ -402,7 +389,7 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
         ZKB_LAUNCH_CHECK(ctx);
     } else {
         k_vf_miller<<<ceil_div(3 * n, LANES), LANES, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
-                                                            (const G2Affine *)(base + o_d), K, dF, d_wf, nn, ni);
+                                                            (const G2Affine *)(base + o_d), K, dF, d_wf, nn, nt);
         ZKB_LAUNCH_CHECK(ctx);
         k_vf_final<<<ceil_div(n, LANES), LANES, 0, st>>>(dF, d_wf, (const Fq12 *)(base + o_ab), K, d_acc, nn);
         ZKB_LAUNCH_CHECK(ctx);
