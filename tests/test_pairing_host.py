@@ -93,3 +93,24 @@ def test_verifier_decisions_match_reference(host):
         got.append(host.hostpair_verify(_p(ab), _p(gam), _p(dlt), _p(abc), ni, _p(x), _p(pr)))
     assert got == g["accept"].tolist()
     assert got == [1, 1, 1, 1, 0, 0, 0, 0]
+
+
+def test_portable_field_path_matches_reference(tmp_path):
+    """fp.cuh's plain-C++ path (tests/host/fp_host.cpp) -- the arithmetic under the host builds above -- against the
+    reference's Fp_model / Fp2_model outputs (fp.tcc:23-685, fp2.tcc:52-136) in tests/golden/fields.npz"""
+    so = str(tmp_path / "libfphost.so")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, os.path.join(HERE, "host", "fp_host.cpp")], check=True)
+    L = C.CDLL(so)
+    g = np.load(os.path.join(GOLD, "fields.npz"))
+    ops = ("add", "sub", "mul", "sqr", "inv", "neg")
+    for field, name in ((0, "fr"), (1, "fq")):
+        a, b = np.ascontiguousarray(g[name + "_a"]), np.ascontiguousarray(g[name + "_b"])
+        for op, on in enumerate(ops):
+            out = np.zeros_like(a)
+            L.hostfp_op(field, op, _p(a), _p(b) if op < 3 else None, _p(out), C.c_size_t(len(a)))
+            assert np.array_equal(out, g[f"{name}_{on}"]), (name, on)
+    a, b = np.ascontiguousarray(g["fq2_a"]), np.ascontiguousarray(g["fq2_b"])
+    for op, on in enumerate(ops):
+        out = np.zeros_like(a)
+        L.hostfq2_op(op, _p(a), _p(b) if op < 3 else None, _p(out), C.c_size_t(len(a)))
+        assert np.array_equal(out, g[f"fq2_{on}"]), on

@@ -1,4 +1,4 @@
-// pairing_coop.cuh -- the pairing of pairing.cuh spread over SIX cooperating lanes.
+// pairing_coop.cuh -- the pairing of pairing.cuh spread over 6 or 18 cooperating lanes.
 //
 // At verification-sized batches (64 proofs) the device is almost empty and the time is one lane's chain of
 // dependent 254-bit products (pairing.cuh: ~9 000 per Miller loop).  The tower arithmetic has 6-way parallelism
@@ -68,18 +68,8 @@ ZKB_HD Fq half(const Fq &a)
 ZKB_HD Fq2 half(const Fq2 &a) { return Fq2{half(a.c0), half(a.c1)}; }
 ZKB_HD Fq2 embed(const Fq &k) { return Fq2{k, Fq::zero()}; } // mul2(a, embed(k)) == mul_fq(a, k)
 
-// operand pair j of the Karatsuba product of A = (A0, A1, A2) and B = (B0, B1, B2) over v:
-// j = 0, 1, 2: (Aj, Bj);  j = 3, 4, 5: (A1 + A2, ..), (A0 + A1, ..), (A0 + A2, ..)
-ZKB_HD void k6_operands(const Fq2 *A, const Fq2 *B, int j, Fq2 &x, Fq2 &y)
-{
-    const int i0 = j < 3 ? j : (j == 3 ? 1 : 0), i1 = j == 4 ? 1 : 2;
-    x = A[i0];
-    y = B[i0];
-    if (j >= 3) {
-        x = x + A[i1];
-        y = y + B[i1];
-    }
-}
+// Karatsuba over v of A = (A0, A1, A2) and B = (B0, B1, B2): operand pair j = 0, 1, 2 is (Aj, Bj); j = 3, 4, 5 are
+// (A1 + A2, B1 + B2), (A0 + A1, B0 + B1), (A0 + A2, B0 + B2) -- the product phases below pick theirs by lane.
 // coefficient c of that product from the six partial products p[0..5]:
 //   c = 0: p0 + xi (p3 - p1 - p2);  c = 1: (p4 - p0 - p1) + xi p2;  c = 2: (p5 - p0 - p2) + p1
 ZKB_HD Fq2 k6_coef(const Fq2 *p, int c)

@@ -10,9 +10,11 @@
 // vk.alpha_g1_beta_g2 limb for limb, AND the three proof points lying on their curves.
 //
 // Parallel shape: the batch is the parallel axis.  Every Miller loop has the same control flow (the loop
-// count is a constant), so the 3 n Miller loops of n proofs run in lock step, one per lane; the n final
-// exponentiations likewise.  The public-input sums input_j * gamma_ABC[j + 1] are one lane per (proof, input).
-// Latency-bound (dependent 254-bit products): built with the out-of-line multiplier.
+// count is a constant), so the 3 n Miller loops of n proofs run in lock step, and the n final exponentiations
+// likewise: one lane each for large batches, 6 or 18 cooperating lanes each (pairing_coop.cuh) while the batch is
+// too small to fill the device.  The public-input sums input_j * gamma_ABC[j + 1] are one lane per
+// (proof, input, 32-bit chunk) over a per-key table.  Latency-bound (dependent 254-bit products): built with the
+// out-of-line multiplier.
 #define ZKB_NOINLINE_MUL 1
 #include "common.cuh"
 #include "pairing_coop.cuh"
@@ -36,8 +38,6 @@ template <class F> __device__ void affine_in(const Affine<F> &a, F &x, F &y)
         y = a.y;
     }
 }
-
-__device__ Fq2 twist_b_of(const PairingConsts &K) { return K.twist_b; }
 
 // Public-input sums with a per-key table: input_j * P_j = sum_c chunk_c * (2^(32 c) P_j), eight 32-bit chunks.
 // The 8 multiples of every gamma_ABC[j + 1] are made once per verification key (k_vf_tab; zkb_verify_batch keeps them
@@ -94,7 +94,7 @@ __global__ void k_vf_miller(const ProofJ *proofs, const G1X *T, const G1Affine *
         const G2J B = ld_vec(&proofs[i].B);
         Fq three = Fq::one();
         three = three + three.dbl();
-        ok = jacobian_well_formed<Fq>(A.X, A.Y, A.Z, three) && jacobian_well_formed<Fq2>(B.X, B.Y, B.Z, twist_b_of(K));
+        ok = jacobian_well_formed<Fq>(A.X, A.Y, A.Z, three) && jacobian_well_formed<Fq2>(B.X, B.Y, B.Z, K.twist_b);
         jac_to_affine<Fq>(A, px, py);
         jac_to_affine<Fq2>(B, qx, qy);
     } else if (which == 1) {
@@ -138,7 +138,7 @@ __global__ void k_pairing(const G1Affine *P, const G2Affine *Q, const PairingCon
     st_vec(out + i, f);
 }
 
-// ---- six lanes per Miller loop / final exponentiation (pairing_coop.cuh) ---------------------------------------
+// ---- NL = 6 or 18 lanes per Miller loop / final exponentiation (pairing_coop.cuh) ---------------------------------
 
 // group t = which * n + i as in k_vf_miller; lanes 0 and 1 prepare the affine G1 / G2 inputs, then the group runs
 // the loop together
@@ -373,7 +373,7 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
         ZKB_LAUNCH_CHECK(ctx);
         if (!same) ctx->vf_abc_host.assign(vk->gamma_ABC_g1, vk->gamma_ABC_g1 + abc_words);
     }
-    // small batches: six lanes per Miller loop / final exponentiation (the device is empty, latency is what counts);
+    // small batches: 18 or 6 lanes per Miller loop / final exponentiation (the device is empty, latency is what counts);
     // large batches: one lane each (fewer instructions in total once every warp slot is busy)
     if (lanes == 18) {
         k_vf_miller_coop<18><<<3 * nn, 32, 0, st>>>((const ProofJ *)(base + o_pr), dT, d_abc, (const G2Affine *)(base + o_g),
