@@ -139,6 +139,28 @@ template <int NL> ZKB_NI void coop_sqr12(Fq2 *out, const Fq2 *a, Fq2 *P)
     COOP_END
 }
 
+// a <- a^2 for a in the cyclotomic subgroup (cyc_sqr12 of pairing.cuh): six products, one per lane.  P: 6 registers.
+// Register l holds z0, z4, z3, z2, z1, z5; the Fq4 pairs are (f0, f4), (f3, f2), (f1, f5).
+template <int NL> ZKB_NI void coop_cyc_sqr12(Fq2 *a, Fq2 *P)
+{
+    COOP_FOR6(l)
+    const int k = l >> 1; // pair k: lane 2k makes m = x y, lane 2k + 1 makes n = (x + y)(x + xi y)
+    const Fq2 x = a[k == 0 ? 0 : k == 1 ? 3 : 1], y = a[k == 0 ? 4 : k == 1 ? 2 : 5];
+    const bool second = l & 1;
+    P[l] = mul2(sel(second, x + y, x), sel(second, x + mul_xi(y), y));
+    COOP_END
+    COOP_FOR6(l)
+    // register l takes: 0: 3 te(0) - 2z;  1: 3 te(1) - 2z;  2: 3 te(2) - 2z;  3: 3 xi to(2) + 2z;  4: 3 to(0) + 2z;  5: 3 to(1) + 2z
+    const bool even = l < 3;
+    const int k = even ? l : (l == 3 ? 2 : l - 4);
+    const Fq2 m = P[2 * k], n = P[2 * k + 1], z = a[l];
+    const Fq2 xm = mul_xi(m);
+    const Fq2 t = sel(even, n - m - xm, sel(l == 3, xm.dbl(), m.dbl()));
+    const Fq2 t3 = t.dbl() + t, z2 = z.dbl();
+    a[l] = sel(even, t3 - z2, t3 + z2);
+    COOP_END
+}
+
 // f = f * (e0 + eVV v^2 + eVW v w), the (already scaled) line value.  P: 14 scratch registers.
 template <int NL> ZKB_NI void coop_mul12_line(Fq2 *f, const Fq2 *L /* e0, eVW, eVV */, Fq2 *P)
 {
@@ -333,7 +355,7 @@ template <int NL> ZKB_NI void coop_exp_by_neg_z(Fq2 *out, const Fq2 *a, Fq2 *T)
     const uint64_t z = 0x44e992b44a6909f1ull;
     coop_copy12<NL>(out, a);
     for (int i = 61; i >= 0; i--) {
-        coop_sqr12<NL>(out, out, T);
+        coop_cyc_sqr12<NL>(out, T);
         if ((z >> i) & 1) coop_mul12<NL>(out, out, a, T);
     }
     coop_conj12<NL>(out, out);
@@ -354,11 +376,14 @@ template <int NL> ZKB_NI void coop_final_exponentiation(Fq2 *S, const PairingCon
     coop_mul12<NL>(m, u, t, T);
     // hard part (see final_exponentiation in pairing.cuh)
     coop_exp_by_neg_z<NL>(mz, m, T);          // m^-z
-    coop_sqr12<NL>(m2z, mz, T);               // m^-2z
-    coop_sqr12<NL>(t, m2z, T);
+    coop_copy12<NL>(m2z, mz);
+    coop_cyc_sqr12<NL>(m2z, T);               // m^-2z
+    coop_copy12<NL>(t, m2z);
+    coop_cyc_sqr12<NL>(t, T);
     coop_mul12<NL>(m6z, t, m2z, T);           // m^-6z
     coop_exp_by_neg_z<NL>(m6z2, m6z, T);      // m^(6z^2)
-    coop_sqr12<NL>(t, m6z2, T);
+    coop_copy12<NL>(t, m6z2);
+    coop_cyc_sqr12<NL>(t, T);
     coop_exp_by_neg_z<NL>(u, t, T);
     coop_conj12<NL>(u, u);                    // m^(12z^3)
     coop_mul12<NL>(a, u, m6z2, T);
