@@ -20,13 +20,18 @@
 #ifndef ZKB_LIBSNARK_HPP
 #define ZKB_LIBSNARK_HPP
 
+#include <array>
 #include <cstring>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <set>
+#include <sstream>
 #include <stdexcept>
 #include <string>
 #include <vector>
+
+#include <openssl/sha.h>
 
 #include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
 #include <libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.hpp>
@@ -118,6 +123,35 @@ inline void pack_matrix(const libsnark::r1cs_constraint_system<FrT> &cs, int whi
     }
 }
 
+/* points the zkb_key_desc of `k` at its arrays (after they have their final sizes) */
+inline void finish_desc(KeyArrays &k, size_t nc, size_t nv, size_t ni, size_t nb, size_t nh)
+{
+    zkb_key_desc &d = k.desc;
+    memset(&d, 0, sizeof(d));
+    d.num_constraints = nc;
+    d.num_variables = nv;
+    d.num_inputs = ni;
+    zkb_csr *m[3] = {&d.A, &d.B, &d.C};
+    for (int w = 0; w < 3; w++) {
+        m[w]->row_ptr = k.row_ptr[w].data();
+        m[w]->col = k.col[w].data();
+        m[w]->coeff = k.coeff[w].data();
+    }
+    d.alpha_g1 = &k.singles[0];
+    d.beta_g1 = &k.singles[8];
+    d.delta_g1 = &k.singles[16];
+    d.beta_g2 = &k.singles[24];
+    d.delta_g2 = &k.singles[40];
+    d.A_query = k.A.data();
+    d.B_nnz = nb;
+    d.B_index = k.B_idx.data();
+    d.B_g1 = k.B1.data();
+    d.B_g2 = k.B2.data();
+    d.H_size = nh;
+    d.H_query = k.H.data();
+    d.L_query = k.L.data();
+}
+
 inline void pack_proving_key(const libsnark::r1cs_gg_ppzksnark_proving_key<PP> &pk, KeyArrays &k)
 {
     const libsnark::r1cs_constraint_system<FrT> &cs = pk.constraint_system;
@@ -143,31 +177,129 @@ inline void pack_proving_key(const libsnark::r1cs_gg_ppzksnark_proving_key<PP> &
     for (size_t i = 0; i < pk.H_query.size(); i++) put_g1_affine(&k.H[8 * i], pk.H_query[i]);
     k.L.resize(pk.L_query.size() * 8 + 8);
     for (size_t i = 0; i < pk.L_query.size(); i++) put_g1_affine(&k.L[8 * i], pk.L_query[i]);
+    finish_desc(k, cs.num_constraints(), cs.num_variables(), cs.num_inputs(), nb, pk.H_query.size());
+}
 
-    zkb_key_desc &d = k.desc;
-    memset(&d, 0, sizeof(d));
-    d.num_constraints = cs.num_constraints();
-    d.num_variables = cs.num_variables();
-    d.num_inputs = cs.num_inputs();
-    zkb_csr *m[3] = {&d.A, &d.B, &d.C};
-    for (int w = 0; w < 3; w++) {
-        m[w]->row_ptr = k.row_ptr[w].data();
-        m[w]->col = k.col[w].data();
-        m[w]->coeff = k.coeff[w].data();
+/* ---- key import with the square roots left to the GPU ---------------------------------
+ * libsnark_import_pk (zklaim/libsnark_wrapper.cpp:160-168) runs operator>> of r1cs_gg_ppzksnark_proving_key
+ * (r1cs_gg_ppzksnark.tcc:68-88), which recomputes Y = sqrt(X^3 + b) for every element of the key on one host thread
+ * (alt_bn128_g1.cpp:436-450, alt_bn128_g2.cpp:449-463): 7 s for the zklaim key.  This reader walks the same byte stream
+ * with the reference's framing (the build's BINARY_OUTPUT + MONTGOMERY_OUTPUT, point compression on: a G1 element is
+ * is_zero, X (32 bytes), lsb(Y); sizes are decimal + '\n'; sparse_vector.tcc:290-325, knowledge_commitment.tcc:127-134),
+ * collects the abscissas, and hands them to zkb_points_decompress; the constraint system at the end of the stream is
+ * parsed by libsnark's own operator>>. */
+struct PkCursor {
+    const unsigned char *p, *end;
+    bool ok;
+    size_t size_line()
+    {
+        size_t v = 0;
+        bool any = false;
+        while (p < end && *p >= '0' && *p <= '9') {
+            v = v * 10 + (size_t)(*p - '0');
+            p++;
+            any = true;
+        }
+        if (!any || p >= end || *p != '\n') ok = false;
+        else p++;
+        return v;
     }
-    d.alpha_g1 = &k.singles[0];
-    d.beta_g1 = &k.singles[8];
-    d.delta_g1 = &k.singles[16];
-    d.beta_g2 = &k.singles[24];
-    d.delta_g2 = &k.singles[40];
-    d.A_query = k.A.data();
-    d.B_nnz = nb;
-    d.B_index = k.B_idx.data();
-    d.B_g1 = k.B1.data();
-    d.B_g2 = k.B2.data();
-    d.H_size = pk.H_query.size();
-    d.H_query = k.H.data();
-    d.L_query = k.L.data();
+    void point(size_t words, std::vector<uint64_t> &x, std::vector<uint8_t> &flags)
+    {
+        if (!ok || (size_t)(end - p) < 2 + 8 * words) {
+            ok = false;
+            return;
+        }
+        const unsigned zero = (unsigned)(p[0] - '0'), lsb = (unsigned)(p[1 + 8 * words] - '0');
+        if (zero > 1 || lsb > 1) ok = false;
+        const size_t o = x.size();
+        x.resize(o + words);
+        memcpy(&x[o], p + 1, 8 * words);
+        flags.push_back((uint8_t)(lsb | (zero << 1)));
+        p += 2 + 8 * words;
+    }
+};
+
+/* fills `k` from the serialised proving key; *nv / *ni = variables / inputs of its constraint system */
+inline void import_pk_deferred(zkb_ctx *ctx, const unsigned char *pk, size_t size, KeyArrays &k, size_t *nv_out, size_t *ni_out)
+{
+#if !defined(BINARY_OUTPUT) || !defined(MONTGOMERY_OUTPUT) || defined(NO_PT_COMPRESSION)
+#error "the deferred key import reads the BINARY_OUTPUT + MONTGOMERY_OUTPUT + compressed-point stream zklaim is built with"
+#endif
+    PkCursor c{pk, pk + size, true};
+    std::vector<uint64_t> x1, x2;
+    std::vector<uint8_t> f1, f2;
+    /* r1cs_gg_ppzksnark.tcc:68-88: alpha_g1, beta_g1, beta_g2, delta_g1, delta_g2, A, B, H, L, constraint system */
+    c.point(4, x1, f1);
+    c.point(4, x1, f1);
+    c.point(8, x2, f2);
+    c.point(4, x1, f1);
+    c.point(8, x2, f2);
+    const size_t nA = c.size_line();
+    if (c.ok) x1.reserve(4 * (3 + nA));
+    for (size_t i = 0; c.ok && i < nA; i++) c.point(4, x1, f1);
+    c.size_line(); /* B_query.domain_size_ */
+    const size_t nidx = c.size_line();
+    k.B_idx.assign(nidx + 1, 0);
+    for (size_t i = 0; c.ok && i < nidx; i++) k.B_idx[i] = (uint32_t)c.size_line();
+    const size_t nB = c.size_line();
+    if (nB != nidx) c.ok = false;
+    for (size_t i = 0; c.ok && i < nB; i++) { /* knowledge_commitment<G2, G1>: g then h */
+        c.point(8, x2, f2);
+        c.point(4, x1, f1);
+    }
+    const size_t nH = c.size_line();
+    for (size_t i = 0; c.ok && i < nH; i++) c.point(4, x1, f1);
+    const size_t nL = c.size_line();
+    for (size_t i = 0; c.ok && i < nL; i++) c.point(4, x1, f1);
+    if (!c.ok) throw std::runtime_error("zkb key import: the proving key stream does not have libsnark's framing");
+    libsnark::r1cs_constraint_system<FrT> cs;
+    {
+        std::istringstream in(std::string((const char *)c.p, (size_t)(c.end - c.p)));
+        in >> cs;
+        if (in.fail()) throw std::runtime_error("zkb key import: constraint system unreadable");
+    }
+    for (int w = 0; w < 3; w++) pack_matrix(cs, w, k);
+    /* the roots, on the GPU */
+    const size_t n1 = f1.size(), n2 = f2.size();
+    std::vector<uint64_t> p1(8 * n1 + 8), p2(16 * n2 + 16);
+    if (zkb_points_decompress(ctx, ZKB_G1, x1.data(), f1.data(), n1, p1.data(), NULL) != ZKB_OK ||
+        zkb_points_decompress(ctx, ZKB_G2, x2.data(), f2.data(), n2, p2.data(), NULL) != ZKB_OK)
+        throw std::runtime_error(std::string("zkb_points_decompress failed: ") + zkb_last_error(ctx));
+    /* G1 order: alpha, beta, delta, A (nA), B.h (nB), H (nH), L (nL); G2 order: beta, delta, B.g (nB) */
+    k.singles.resize(8 * 3 + 16 * 2);
+    memcpy(&k.singles[0], &p1[0], 3 * 64);
+    memcpy(&k.singles[24], &p2[0], 2 * 128);
+    const uint64_t *q = &p1[3 * 8];
+    k.A.assign(q, q + 8 * nA);
+    q += 8 * nA;
+    k.B1.assign(8 * nB + 8, 0);
+    memcpy(k.B1.data(), q, 64 * nB);
+    q += 8 * nB;
+    k.H.assign(8 * nH + 8, 0);
+    memcpy(k.H.data(), q, 64 * nH);
+    q += 8 * nH;
+    k.L.assign(8 * nL + 8, 0);
+    memcpy(k.L.data(), q, 64 * nL);
+    k.B2.assign(16 * nB + 16, 0);
+    memcpy(k.B2.data(), &p2[2 * 16], 128 * nB);
+    finish_desc(k, cs.num_constraints(), cs.num_variables(), cs.num_inputs(), nB, nH);
+    *nv_out = cs.num_variables();
+    *ni_out = cs.num_inputs();
+}
+
+/* identity of a serialised key: SHA-256 of the bytes and their number */
+struct KeyId {
+    std::array<unsigned char, 32> digest;
+    size_t size;
+    bool operator<(const KeyId &o) const { return size != o.size ? size < o.size : digest < o.digest; }
+};
+inline KeyId key_id_of_bytes(const void *p, size_t n)
+{
+    KeyId id;
+    id.size = n;
+    SHA256((const unsigned char *)p, n, id.digest.data());
+    return id;
 }
 
 /* 64-bit FNV-1a */
@@ -178,41 +310,48 @@ inline uint64_t fnv1a(const void *p, size_t n, uint64_t h = 0xcbf29ce484222325ul
     return h;
 }
 
-/* identifies a proving key without walking all of it: sizes, the five single elements and probes of the queries */
-inline uint64_t key_fingerprint(const libsnark::r1cs_gg_ppzksnark_proving_key<PP> &pk)
+/* identity of an in-memory proving key (the header-only drop-in zkb_bridge::prover has no byte stream to hash): SHA-256
+ * over its sizes and every group element of the key */
+inline KeyId key_fingerprint(const libsnark::r1cs_gg_ppzksnark_proving_key<PP> &pk)
 {
-    uint64_t buf[64];
-    size_t n = 0;
-    buf[n++] = pk.constraint_system.num_constraints();
-    buf[n++] = pk.constraint_system.num_variables();
-    buf[n++] = pk.constraint_system.num_inputs();
-    buf[n++] = pk.A_query.size();
-    buf[n++] = pk.B_query.indices.size();
-    buf[n++] = pk.H_query.size();
-    buf[n++] = pk.L_query.size();
-    uint64_t h = fnv1a(buf, n * 8);
-    auto mix_g1 = [&](const G1T &p) {
-        uint64_t t[8];
-        put_g1_affine(t, p);
-        h = fnv1a(t, 64, h);
+    SHA256_CTX sha;
+    SHA256_Init(&sha);
+    const uint64_t dims[7] = {pk.constraint_system.num_constraints(), pk.constraint_system.num_variables(),
+                              pk.constraint_system.num_inputs(), pk.A_query.size(), pk.B_query.indices.size(),
+                              pk.H_query.size(), pk.L_query.size()};
+    SHA256_Update(&sha, dims, sizeof(dims));
+    auto mix_g1 = [&](const G1T &p) { /* Jacobian limbs as stored: a key is affine-normalised (Z = 1 or 0) */
+        uint64_t t[12];
+        memcpy(t, p.X.mont_repr.data, 32);
+        memcpy(t + 4, p.Y.mont_repr.data, 32);
+        memcpy(t + 8, p.Z.mont_repr.data, 32);
+        SHA256_Update(&sha, t, sizeof(t));
+    };
+    auto mix_g2 = [&](const G2T &p) {
+        uint64_t t[16];
+        put_g2_affine(t, p);
+        SHA256_Update(&sha, t, sizeof(t));
     };
     mix_g1(pk.alpha_g1);
     mix_g1(pk.beta_g1);
     mix_g1(pk.delta_g1);
-    uint64_t t2[16];
-    put_g2_affine(t2, pk.delta_g2);
-    h = fnv1a(t2, 128, h);
-    if (!pk.A_query.empty()) mix_g1(pk.A_query.back());
-    if (!pk.H_query.empty()) {
-        mix_g1(pk.H_query.front());
-        mix_g1(pk.H_query.back());
-    }
-    if (!pk.L_query.empty()) mix_g1(pk.L_query.back());
-    return h;
+    mix_g2(pk.beta_g2);
+    mix_g2(pk.delta_g2);
+    for (const G1T &p : pk.A_query) mix_g1(p);
+    for (const auto &kc : pk.B_query.values) mix_g1(kc.h);
+    for (const G1T &p : pk.H_query) mix_g1(p);
+    for (const G1T &p : pk.L_query) mix_g1(p);
+    KeyId id;
+    id.size = 0; /* distinguishes object identities from byte-stream identities (size > 0) */
+    SHA256_Final(id.digest.data(), &sha);
+    return id;
 }
 
-/* One zkb context per device plus the uploaded keys, for the lifetime of the process.  zklaim's bridge is
- * single-threaded (libsnark_wrapper.cpp re-initialises the curve globals per call), so is this cache. */
+/* The devices this process proves on and the keys uploaded to them, for the lifetime of the process.
+ * Devices: ZKB_DEVICES="0,2,3" (a list), else ZKB_DEVICE=n (one device; what a one-process-per-GPU launcher sets), else
+ * every visible device (CUDA_VISIBLE_DEVICES applies).  zkb_pool (include/zkb.h) gives one context per device.
+ * Thread safety: the maps are guarded by mu(); a zkb_ctx serves one host thread at a time (zkb.h), so callers hold
+ * gpu() around every zkb_* call -- host-side witness generation of concurrent callers overlaps, GPU use is serialised. */
 class Session {
   public:
     static Session &get()
@@ -220,50 +359,109 @@ class Session {
         static Session s;
         return s;
     }
-    zkb_ctx *ctx()
+    std::mutex &gpu() { return gpu_mu_; }
+    zkb_pool *pool()
     {
-        if (!ctx_) {
-            const char *dev = getenv("ZKB_DEVICE");
-            if (zkb_init(dev ? atoi(dev) : 0, &ctx_) != ZKB_OK)
-                throw std::runtime_error(std::string("zkb_init failed: ") + zkb_last_error(NULL));
-        }
-        return ctx_;
+        std::lock_guard<std::mutex> g(mu_);
+        return pool_locked();
     }
-    /* returns the cached device key for `id`, or uploads it with `make` */
-    template <class PackFn> const zkb_key *key(uint64_t id, PackFn pack)
+    zkb_ctx *ctx() { return zkb_pool_ctx(pool(), 0); }
+    int devices() { return zkb_pool_size(pool()); }
+    /* returns the cached device keys for `id`, or uploads them (every device of the pool) with `pack` */
+    template <class PackFn> zkb_key_set *keys(const KeyId &id, PackFn pack)
     {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            auto it = keys_.find(id);
+            if (it != keys_.end()) return it->second;
+        }
+        std::unique_ptr<KeyArrays> arrays(new KeyArrays());
+        pack(*arrays); /* may use the GPU (deferred import): outside mu_, under the caller's gpu() lock */
+        std::lock_guard<std::mutex> g(mu_);
         auto it = keys_.find(id);
         if (it != keys_.end()) return it->second;
-        std::unique_ptr<KeyArrays> arrays(new KeyArrays());
-        pack(*arrays);
-        zkb_key *k = NULL;
-        if (zkb_key_upload(ctx(), &arrays->desc, &k) != ZKB_OK)
-            throw std::runtime_error(std::string("zkb_key_upload failed: ") + zkb_last_error(ctx_));
+        zkb_key_set *k = NULL;
+        if (zkb_pool_key_upload(pool_locked(), &arrays->desc, &k) != ZKB_OK)
+            throw std::runtime_error(std::string("zkb_pool_key_upload failed: ") + zkb_pool_last_error(pool_));
         keys_[id] = k;
         return k;
     }
-    bool has_key(uint64_t id) const { return keys_.count(id) != 0; }
-    /* first witness seen for a key: size its MSM windows for that witness's 0 / 1 statistics (zkb_key_tune) */
-    void tune_once(const zkb_key *key, const uint64_t *w)
+    template <class PackFn> const zkb_key *key(const KeyId &id, PackFn pack) { return zkb_pool_key(keys(id, pack), 0); }
+    bool has_key(const KeyId &id)
     {
-        if (!tuned_.insert(key).second) return;
-        if (zkb_key_tune(ctx(), const_cast<zkb_key *>(key), w) != ZKB_OK)
-            throw std::runtime_error(std::string("zkb_key_tune failed: ") + zkb_last_error(ctx_));
+        std::lock_guard<std::mutex> g(mu_);
+        return keys_.count(id) != 0;
+    }
+    /* first witness seen for a key: size its MSM windows for that witness's 0 / 1 statistics (zkb_key_tune) */
+    void tune_once(zkb_key_set *ks, const uint64_t *w)
+    {
+        std::lock_guard<std::mutex> g(mu_);
+        if (!tuned_.insert(ks).second) return;
+        if (zkb_pool_key_tune(pool_locked(), ks, w) != ZKB_OK)
+            throw std::runtime_error(std::string("zkb_key_tune failed: ") + zkb_pool_last_error(pool_));
+    }
+    /* SHA-256 identity of a serialised key, remembered per (address, size) of the caller's buffer: the 20 MB of a zklaim
+     * key are hashed once, later calls re-check sampled probes of the buffer */
+    KeyId id_of_buffer(const unsigned char *p, size_t n)
+    {
+        const uint64_t probe = probe_of(p, n);
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            auto it = seen_.find(std::make_pair((const void *)p, n));
+            if (it != seen_.end() && it->second.first == probe) return it->second.second;
+        }
+        const KeyId id = key_id_of_bytes(p, n);
+        std::lock_guard<std::mutex> g(mu_);
+        if (seen_.size() > 64) seen_.clear();
+        seen_[std::make_pair((const void *)p, n)] = std::make_pair(probe, id);
+        return id;
     }
     void clear()
     {
-        for (auto &kv : keys_) zkb_key_free(kv.second);
+        std::lock_guard<std::mutex> g(mu_);
+        for (auto &kv : keys_) zkb_pool_key_free(kv.second);
         keys_.clear();
         tuned_.clear();
-        if (ctx_) zkb_shutdown(ctx_);
-        ctx_ = NULL;
+        seen_.clear();
+        if (pool_) zkb_pool_shutdown(pool_);
+        pool_ = NULL;
     }
     ~Session() { clear(); }
 
   private:
-    zkb_ctx *ctx_ = NULL;
-    std::map<uint64_t, zkb_key *> keys_;
-    std::set<const zkb_key *> tuned_;
+    zkb_pool *pool_locked()
+    {
+        if (pool_) return pool_;
+        std::vector<int> ids;
+        if (const char *list = getenv("ZKB_DEVICES")) {
+            for (const char *q = list; *q;) {
+                char *e;
+                const long v = strtol(q, &e, 10);
+                if (e == q) break;
+                ids.push_back((int)v);
+                q = *e == ',' ? e + 1 : e;
+            }
+        } else if (const char *one = getenv("ZKB_DEVICE")) {
+            ids.push_back(atoi(one));
+        }
+        if (zkb_pool_init(ids.empty() ? NULL : ids.data(), (int)ids.size(), &pool_) != ZKB_OK)
+            throw std::runtime_error(std::string("zkb_pool_init failed: ") + zkb_last_error(NULL));
+        return pool_;
+    }
+    static uint64_t probe_of(const unsigned char *p, size_t n)
+    {
+        uint64_t h = fnv1a(&n, sizeof(n));
+        const size_t edge = n < 2048 ? n : 2048;
+        h = fnv1a(p, edge, h);
+        h = fnv1a(p + n - edge, edge, h);
+        for (size_t i = 1; i < 64; i++) h = fnv1a(p + (n / 64) * i, n - (n / 64) * i < 64 ? n - (n / 64) * i : 64, h);
+        return h;
+    }
+    std::mutex mu_, gpu_mu_;
+    zkb_pool *pool_ = NULL;
+    std::map<KeyId, zkb_key_set *> keys_;
+    std::set<const zkb_key_set *> tuned_;
+    std::map<std::pair<const void *, size_t>, std::pair<uint64_t, KeyId>> seen_;
 };
 
 inline libsnark::r1cs_gg_ppzksnark_proof<PP> wrap_proof(const zkb_proof &p)
@@ -344,6 +542,7 @@ inline std::vector<bool> verifier_strong_IC_batch(const libsnark::r1cs_gg_ppzksn
     }
     std::vector<int32_t> acc(live.size(), 0);
     zkb_ctx *ctx = Session::get().ctx();
+    std::lock_guard<std::mutex> gpu(Session::get().gpu());
     const int rc = zkb_verify_batch(ctx, &a.desc, x.data(), pr.data(), live.size(), acc.data());
     if (rc != ZKB_OK) throw std::runtime_error(std::string("zkb_verify_batch failed: ") + zkb_last_error(ctx));
     for (size_t k = 0; k < live.size(); k++) res[live[k]] = acc[k] != 0;
@@ -368,12 +567,17 @@ inline void pack_assignment(const std::vector<FrT> &primary, const std::vector<F
 }
 
 /* the prover with the blinding scalars given (tests fix them; the drop-in below draws them) */
-inline libsnark::r1cs_gg_ppzksnark_proof<PP> prover_with_rs(const zkb_key *key, const std::vector<FrT> &primary,
+inline libsnark::r1cs_gg_ppzksnark_proof<PP> prover_with_rs(zkb_key_set *keys, const std::vector<FrT> &primary,
                                                            const std::vector<FrT> &auxiliary, const FrT &r, const FrT &s)
 {
+    size_t nv = 0;
+    const zkb_key *key = zkb_pool_key(keys, 0);
+    if (zkb_key_num_variables(key, &nv) != ZKB_OK || nv != primary.size() + auxiliary.size())
+        throw std::runtime_error("zkb prover: the assignment does not have the key's number of variables");
     std::vector<uint64_t> w(4 * (primary.size() + auxiliary.size()));
     pack_assignment(primary, auxiliary, w.data());
-    Session::get().tune_once(key, w.data());
+    std::lock_guard<std::mutex> gpu(Session::get().gpu());
+    Session::get().tune_once(keys, w.data());
     zkb_proof out;
     zkb_ctx *ctx = Session::get().ctx();
     const int rc = zkb_prove(ctx, key, w.data(), (const uint64_t *)r.mont_repr.data, (const uint64_t *)s.mont_repr.data, &out, NULL);
@@ -388,9 +592,9 @@ libsnark::r1cs_gg_ppzksnark_proof<ppT> prover(const libsnark::r1cs_gg_ppzksnark_
                                               const libsnark::r1cs_gg_ppzksnark_auxiliary_input<ppT> &auxiliary_input)
 {
     static_assert(std::is_same<ppT, PP>::value, "the zkb backend implements alt_bn128 only");
-    const zkb_key *key = Session::get().key(key_fingerprint(pk), [&](KeyArrays &k) { pack_proving_key(pk, k); });
+    zkb_key_set *keys = Session::get().keys(key_fingerprint(pk), [&](KeyArrays &k) { pack_proving_key(pk, k); });
     const FrT r = FrT::random_element(), s = FrT::random_element(); /* r1cs_gg_ppzksnark.tcc:418-419 */
-    return prover_with_rs(key, primary_input, auxiliary_input, r, s);
+    return prover_with_rs(keys, primary_input, auxiliary_input, r, s);
 }
 
 /* ---- the generator (include/zkb.h zkb_setup) ---------------------------------- */
@@ -474,6 +678,7 @@ inline libsnark::r1cs_gg_ppzksnark_keypair<PP> generator_with_randomness(const l
     o.gamma_ABC_g1 = abc.data();
     int swapped = 0;
     zkb_ctx *ctx = Session::get().ctx();
+    std::unique_lock<std::mutex> gpu(Session::get().gpu());
     if (zkb_setup(ctx, &d, &o, &swapped) != ZKB_OK) throw std::runtime_error(std::string("zkb_setup failed: ") + zkb_last_error(ctx));
 
     libsnark::r1cs_constraint_system<FrT> cs(r1cs);
@@ -500,6 +705,7 @@ inline libsnark::r1cs_gg_ppzksnark_keypair<PP> generator_with_randomness(const l
     uint64_t ab[48];
     if (zkb_pairing(ctx, o.alpha_g1, o.beta_g2, 1, 1, ab) != ZKB_OK)
         throw std::runtime_error(std::string("zkb_pairing failed: ") + zkb_last_error(ctx));
+    gpu.unlock();
     libsnark::r1cs_gg_ppzksnark_verification_key<PP> vk(get_fq12(ab), gamma_g2, delta_g2, gamma_ABC_g1);
     G2T delta_g2_pk = delta_g2;
     libsnark::r1cs_gg_ppzksnark_proving_key<PP> pk(std::move(alpha_g1), std::move(beta_g1), std::move(beta_g2), std::move(delta_g1),

@@ -11,8 +11,9 @@
  *            -> r1cs_gg_ppzksnark_prover<ppT>(pk, primary, auxiliary)   snark.cpp:126
  *
  * re-stated as zkb_libsnark_prove() with the prover call replaced by zkb_bridge::prover (zkb_libsnark.hpp)
- * and the 7-second key import (libsnark_import_pk, :228-230) done once per key instead of once per proof:
- * the device key is cached under a hash of ctx->pk.  Same contract: 0 = ok, 1 = witness unsatisfied;
+ * and the 7-second key import (libsnark_import_pk, :228-230) done once per key instead of once per proof -- and its
+ * square roots on the GPU (import_pk_deferred): the device keys are cached under the SHA-256 of ctx->pk.
+ * Same contract: 0 = ok, 1 = witness unsatisfied;
  * ctx->proof is malloc'ed by the callee (:178-179).
  *
  * The zkbr_* functions at the end are measurement / test support (used by bench.py and tests/): they drive
@@ -32,24 +33,64 @@ using namespace zkb_bridge;
 namespace {
 
 struct CachedKey {
-    const zkb_key *key = NULL;
+    zkb_key_set *keys = NULL; /* one replica per device of the session's pool */
     size_t num_variables = 0, num_inputs = 0;
+    const zkb_key *key() const { return zkb_pool_key(keys, 0); }
 };
-std::map<uint64_t, CachedKey> g_keys_by_pk_hash;
+std::mutex g_cache_mu;
+std::map<KeyId, CachedKey> g_keys_by_id;
 
-/* device key for the serialised proving key in ctx->pk: imported and uploaded on first use only */
-CachedKey &key_for_ctx(zklaim_ctx *ctx)
+bool host_import_enabled()
 {
-    const uint64_t h = fnv1a(ctx->pk, ctx->pk_size);
-    auto it = g_keys_by_pk_hash.find(h);
-    if (it != g_keys_by_pk_hash.end()) return it->second;
-    r1cs_gg_ppzksnark_proving_key<ppT> pk;
-    libsnark_import_pk(&pk, ctx->pk, ctx->pk_size);
+    const char *e = getenv("ZKB_HOST_IMPORT"); /* 1: the reference's own importer (one square root per point on the host) */
+    return e && atoi(e) != 0;
+}
+
+/* device keys for the serialised proving key in ctx->pk: imported and uploaded on first use only.  The identity of a key
+ * is the SHA-256 of its bytes (+ their number).  Import = libsnark's framing read here, the square roots of the
+ * compressed points on the GPU (import_pk_deferred): 7.3 s -> a fraction of a second for the zklaim key. */
+CachedKey key_for_ctx(zklaim_ctx *ctx)
+{
+    if (!ctx->pk || !ctx->pk_size) throw std::runtime_error("no proving key in the context");
+    const KeyId id = Session::get().id_of_buffer(ctx->pk, ctx->pk_size);
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        auto it = g_keys_by_id.find(id);
+        if (it != g_keys_by_id.end()) return it->second;
+    }
     CachedKey ck;
-    ck.key = Session::get().key(h, [&](KeyArrays &k) { pack_proving_key(pk, k); });
+    ck.keys = Session::get().keys(id, [&](KeyArrays &k) {
+        if (host_import_enabled()) {
+            r1cs_gg_ppzksnark_proving_key<ppT> pk;
+            libsnark_import_pk(&pk, ctx->pk, ctx->pk_size);
+            pack_proving_key(pk, k);
+            ck.num_variables = pk.constraint_system.num_variables();
+            ck.num_inputs = pk.constraint_system.num_inputs();
+        } else {
+            std::lock_guard<std::mutex> gpu(Session::get().gpu());
+            import_pk_deferred(Session::get().ctx(), ctx->pk, ctx->pk_size, k, &ck.num_variables, &ck.num_inputs);
+        }
+    });
+    if (!ck.num_variables) { /* another thread uploaded the key in the meantime: ask the device key */
+        zkb_key_num_variables(ck.key(), &ck.num_variables);
+    }
+    std::lock_guard<std::mutex> g(g_cache_mu);
+    auto it = g_keys_by_id.find(id);
+    if (it != g_keys_by_id.end()) return it->second;
+    return g_keys_by_id[id] = ck;
+}
+
+/* a key this process has just made (zkb_libsnark_trusted_setup): upload it from the objects at hand, so that the first
+ * proof under it does not serialise -> parse -> decompress what is already in memory */
+void register_fresh_key(zklaim_ctx *ctx, const r1cs_gg_ppzksnark_proving_key<ppT> &pk)
+{
+    const KeyId id = Session::get().id_of_buffer(ctx->pk, ctx->pk_size);
+    CachedKey ck;
+    ck.keys = Session::get().keys(id, [&](KeyArrays &k) { pack_proving_key(pk, k); });
     ck.num_variables = pk.constraint_system.num_variables();
     ck.num_inputs = pk.constraint_system.num_inputs();
-    return g_keys_by_pk_hash[h] = ck;
+    std::lock_guard<std::mutex> g(g_cache_mu);
+    g_keys_by_id[id] = ck;
 }
 
 /* host half of generate_proof exactly as the reference runs it (snark.cpp:113-124): circuit + constraints + witness +
@@ -161,6 +202,7 @@ int zkb_libsnark_trusted_setup(zklaim_ctx *ctx)
         r1cs_gg_ppzksnark_keypair<ppT> keypair = zkb_bridge::generator<ppT>(cs);
         ctx->vk_size = libsnark_export_vk(keypair.vk, &ctx->vk);
         ctx->pk_size = libsnark_export_pk(keypair.pk, &ctx->pk);
+        register_fresh_key(ctx, keypair.pk);
         return 0;
     } catch (const std::exception &e) {
         fprintf(stderr, "zkb_libsnark_trusted_setup: %s\n", e.what());
@@ -168,25 +210,35 @@ int zkb_libsnark_trusted_setup(zklaim_ctx *ctx)
     }
 }
 
-/* Replacement of libsnark_prove (zklaim/zklaim.h:259, libsnark_wrapper.cpp:218-250). */
+/* Replacement of libsnark_prove (zklaim/zklaim.h:259, libsnark_wrapper.cpp:218-250).  Callable from several host
+ * threads: witness generation runs concurrently, the GPU is used by one caller at a time. */
 int zkb_libsnark_prove(zklaim_ctx *ctx)
 {
     StdoutMute mute;
     ppT::init_public_params();
     try {
-        CachedKey &ck = key_for_ctx(ctx);
+        const CachedKey ck = key_for_ctx(ctx);
         std::vector<FrT> primary, auxiliary;
         if (!build_witness(ctx, primary, auxiliary)) return 1;
+        /* a context whose payload count does not fit the circuit of its proving key (zklaim_gadget sizes the circuit from
+         * num_of_payloads) would make the device read past the assignment */
+        if (primary.size() + auxiliary.size() != ck.num_variables) return -2;
         const FrT r = FrT::random_element(), s = FrT::random_element();
         std::vector<uint64_t> w(4 * (primary.size() + auxiliary.size()));
         pack_assignment(primary, auxiliary, w.data());
-        Session::get().tune_once(ck.key, w.data());
         zkb_proof out;
-        zkb_ctx *z = Session::get().ctx();
-        const int rc = zkb_prove(z, ck.key, w.data(), (const uint64_t *)r.mont_repr.data, (const uint64_t *)s.mont_repr.data, &out, NULL);
+        int rc;
+        std::string err;
+        {
+            std::lock_guard<std::mutex> gpu(Session::get().gpu());
+            Session::get().tune_once(ck.keys, w.data());
+            zkb_ctx *z = Session::get().ctx();
+            rc = zkb_prove(z, ck.key(), w.data(), (const uint64_t *)r.mont_repr.data, (const uint64_t *)s.mont_repr.data, &out, NULL);
+            if (rc != ZKB_OK) err = zkb_last_error(z);
+        }
         if (rc == ZKB_ERR_UNSAT) return 1; /* libsnark_wrapper.cpp:233-240: witness unsatisfied */
         if (rc != ZKB_OK) {
-            fprintf(stderr, "zkb_prove: %s\n", zkb_last_error(z));
+            fprintf(stderr, "zkb_prove: %s\n", err.c_str());
             return -1;
         }
         ctx->proof_size = libsnark_export_proof(wrap_proof(out), &ctx->proof);
@@ -197,23 +249,31 @@ int zkb_libsnark_prove(zklaim_ctx *ctx)
     }
 }
 
-/* `n` credentials that share one proving key: witnesses on the host, one batched GPU call. */
-int zkb_libsnark_prove_batch(zklaim_ctx **ctxs, size_t n)
+/* `n` credentials that share one proving key: witnesses on the host (all host threads), then the batch is split over
+ * every device of the session (zkb_pool_prove_batch: one host thread and one proof stream per GPU).
+ * results (optional, n entries): what libsnark_prove would have returned for credential i -- 0 = proof written to
+ * ctxs[i]->proof, 1 = its witness does not satisfy the constraint system (no proof).  Returns 0 when every credential
+ * got a proof, 1 when at least one was unsatisfied (the others still have theirs), < 0 when the call itself failed
+ * (-2: a context with a different proving key or payload count than ctxs[0]). */
+int zkb_libsnark_prove_batch_ex(zklaim_ctx **ctxs, size_t n, int *results)
 {
     if (!n) return 0;
     StdoutMute mute;
     ppT::init_public_params();
     try {
-        CachedKey &ck = key_for_ctx(ctxs[0]);
+        for (size_t i = 1; i < n; i++) /* one key for the whole batch, as verify_batch requires of the vk */
+            if (ctxs[i]->pk_size != ctxs[0]->pk_size || (ctxs[i]->pk != ctxs[0]->pk && memcmp(ctxs[i]->pk, ctxs[0]->pk, ctxs[0]->pk_size)))
+                return -2;
+        const CachedKey ck = key_for_ctx(ctxs[0]);
         const size_t nv = ck.num_variables;
         std::vector<uint64_t> w(n * nv * 4), r(n * 4), s(n * 4);
+        std::vector<int> res(n, 0);
         int bad = 0;
 #pragma omp parallel for schedule(dynamic, 1)
         for (size_t i = 0; i < n; i++) {
             std::vector<FrT> primary, auxiliary;
-            if (!build_witness(ctxs[i], primary, auxiliary)) {
-#pragma omp atomic write
-                bad = 1;
+            if (!build_witness(ctxs[i], primary, auxiliary)) { /* only with ZKB_HOST_CHECK=1 */
+                res[i] = 1;
                 continue;
             }
             if (primary.size() + auxiliary.size() != nv) {
@@ -223,24 +283,52 @@ int zkb_libsnark_prove_batch(zklaim_ctx **ctxs, size_t n)
             }
             pack_assignment(primary, auxiliary, &w[i * nv * 4]);
         }
-        if (bad) return bad == 1 ? 1 : -2;
+        if (bad) return -2;
+        /* credentials the host check rejected keep a zero assignment: the device reports them unsatisfied as well */
         for (size_t i = 0; i < n; i++) {
             put_fr(&r[4 * i], FrT::random_element());
             put_fr(&s[4 * i], FrT::random_element());
         }
-        Session::get().tune_once(ck.key, w.data());
         std::vector<zkb_proof> out(n);
-        zkb_ctx *z = Session::get().ctx();
-        const int rc = zkb_prove_batch(z, ck.key, n, w.data(), r.data(), s.data(), out.data());
-        if (rc == ZKB_ERR_UNSAT) return 1;
-        if (rc != ZKB_OK) {
-            fprintf(stderr, "zkb_prove_batch: %s\n", zkb_last_error(z));
+        std::vector<int32_t> status(n, 0);
+        int rc;
+        std::string err;
+        {
+            std::lock_guard<std::mutex> gpu(Session::get().gpu());
+            size_t first_ok = 0;
+            while (first_ok < n && res[first_ok]) first_ok++;
+            if (first_ok < n) Session::get().tune_once(ck.keys, &w[first_ok * nv * 4]);
+            zkb_pool *pool = Session::get().pool();
+            rc = zkb_pool_prove_batch(pool, ck.keys, n, w.data(), r.data(), s.data(), out.data(), status.data());
+            if (rc != ZKB_OK) err = zkb_pool_last_error(pool);
+        }
+        if (rc != ZKB_OK && rc != ZKB_ERR_UNSAT) {
+            fprintf(stderr, "zkb_pool_prove_batch: %s\n", err.c_str());
             return -1;
         }
-        for (size_t i = 0; i < n; i++) ctxs[i]->proof_size = libsnark_export_proof(wrap_proof(out[i]), &ctxs[i]->proof);
-        return 0;
+        int any = 0;
+        for (size_t i = 0; i < n; i++) {
+            if (status[i] != ZKB_OK) res[i] = 1;
+            if (res[i] == 0) ctxs[i]->proof_size = libsnark_export_proof(wrap_proof(out[i]), &ctxs[i]->proof);
+            any |= res[i];
+            if (results) results[i] = res[i];
+        }
+        return any ? 1 : 0;
     } catch (const std::exception &e) {
         fprintf(stderr, "zkb_libsnark_prove_batch: %s\n", e.what());
+        return -1;
+    }
+}
+
+int zkb_libsnark_prove_batch(zklaim_ctx **ctxs, size_t n) { return zkb_libsnark_prove_batch_ex(ctxs, n, NULL); }
+
+/* devices the bridge proves on (ZKB_DEVICES / ZKB_DEVICE / all visible) */
+int zkb_libsnark_devices(void)
+{
+    try {
+        return Session::get().devices();
+    } catch (const std::exception &e) {
+        fprintf(stderr, "zkb_libsnark_devices: %s\n", e.what());
         return -1;
     }
 }
@@ -283,7 +371,10 @@ int zkb_libsnark_verify(zklaim_ctx *ctx)
 
 void zkb_bridge_reset(void)
 {
-    g_keys_by_pk_hash.clear();
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        g_keys_by_id.clear();
+    }
     Session::get().clear();
 }
 
@@ -387,7 +478,7 @@ void zkbr_dims(void *h, size_t *dims)
     dims[5] = (size_t)(b->import_upload_s * 1e6);
 }
 
-const zkb_key *zkbr_key(void *h) { return ((Bench *)h)->key.key; }
+const zkb_key *zkbr_key(void *h) { return ((Bench *)h)->key.key(); }
 zkb_ctx *zkbr_ctx(void) { return Session::get().ctx(); }
 
 /* `count` witnesses (num_variables x 4 limbs each) for credentials with salts seed0, seed0 + 1, ...:
@@ -411,7 +502,8 @@ int zkbr_witnesses(void *h, size_t count, uint64_t seed0, uint64_t *w_out)
         pack_assignment(primary, auxiliary, w_out + i * nv * 4);
     }
     if (bad) return bad;
-    Session::get().tune_once(b->key.key, w_out);
+    std::lock_guard<std::mutex> gpu(Session::get().gpu());
+    Session::get().tune_once(b->key.keys, w_out);
     return 0;
 }
 
@@ -518,6 +610,116 @@ int zkbr_verify_roundtrip(void *h, size_t count, uint64_t seed0, size_t tamper, 
         *accepted += gpu_res[i] == 0 ? 1 : 0;
     }
     return agree;
+}
+
+/* `count` credentials of which credential `tamper` has a flipped hash byte, through zkb_libsnark_prove_batch_ex: the
+ * tampered one must be reported unsatisfied (1, no proof), every other one must verify under the reference's
+ * libsnark_verify.  Returns the number of credentials that behaved so (must be `count`); rc_out = the call's result. */
+int zkbr_batch_with_tampered(void *h, size_t count, uint64_t seed0, size_t tamper, int *rc_out)
+{
+    Bench *b = (Bench *)h;
+    std::vector<std::unique_ptr<Credential>> creds;
+    std::vector<zklaim_ctx *> ptrs;
+    for (size_t i = 0; i < count; i++) {
+        creds.emplace_back(new Credential(b->payloads, seed0 + i));
+        zklaim_ctx &c = creds.back()->ctx;
+        if (i == tamper) creds.back()->chain[0].pl.hash[5] ^= 0x10;
+        c.pk_size = b->issuer->ctx.pk_size;
+        c.pk = (unsigned char *)malloc(c.pk_size);
+        memcpy(c.pk, b->issuer->ctx.pk, c.pk_size);
+        c.vk_size = b->issuer->ctx.vk_size;
+        c.vk = (unsigned char *)malloc(c.vk_size);
+        memcpy(c.vk, b->issuer->ctx.vk, c.vk_size);
+        ptrs.push_back(&c);
+    }
+    std::vector<int> res(count, -9);
+    *rc_out = zkb_libsnark_prove_batch_ex(ptrs.data(), count, res.data());
+    int good = 0;
+    for (size_t i = 0; i < count; i++) {
+        if (i == tamper)
+            good += res[i] == 1 && ptrs[i]->proof == NULL ? 1 : 0;
+        else
+            good += res[i] == 0 && ptrs[i]->proof && libsnark_verify(ptrs[i]) == 0 ? 1 : 0;
+    }
+    return good;
+}
+
+/* the issuer's serialised proving key through BOTH importers -- the reference's
+ * libsnark_import_pk (one Tonelli-Shanks root per point on the host) + pack_proving_key, and import_pk_deferred (roots
+ * on the GPU).  Returns 0 when every array of the two flat keys is identical (points at infinity included), else the
+ * index of the first array that differs (1 ..); seconds[0] = reference import, seconds[1] = deferred import. */
+int zkbr_import_check(void *h, double *seconds)
+{
+    Bench *b = (Bench *)h;
+    StdoutMute mute;
+    ppT::init_public_params();
+    try {
+        KeyArrays ref, got;
+        double t = now_s();
+        {
+            r1cs_gg_ppzksnark_proving_key<ppT> pk;
+            libsnark_import_pk(&pk, b->issuer->ctx.pk, b->issuer->ctx.pk_size);
+            pack_proving_key(pk, ref);
+        }
+        seconds[0] = now_s() - t;
+        size_t nv = 0, ni = 0;
+        t = now_s();
+        {
+            std::lock_guard<std::mutex> gpu(Session::get().gpu());
+            import_pk_deferred(Session::get().ctx(), b->issuer->ctx.pk, b->issuer->ctx.pk_size, got, &nv, &ni);
+        }
+        seconds[1] = now_s() - t;
+        if (nv != b->key.num_variables || ni != b->key.num_inputs) return 100;
+        if (ref.singles != got.singles) return 1;
+        if (ref.A != got.A) return 2;
+        if (ref.B_idx != got.B_idx) return 3;
+        if (ref.B1 != got.B1) return 4;
+        if (ref.B2 != got.B2) return 5;
+        if (ref.H != got.H) return 6;
+        if (ref.L != got.L) return 7;
+        for (int w = 0; w < 3; w++)
+            if (ref.row_ptr[w] != got.row_ptr[w] || ref.col[w] != got.col[w] || ref.coeff[w] != got.coeff[w]) return 8 + w;
+        if (ref.desc.B_nnz != got.desc.B_nnz || ref.desc.H_size != got.desc.H_size || ref.desc.num_constraints != got.desc.num_constraints)
+            return 11;
+        return 0;
+    } catch (const std::exception &e) {
+        fprintf(stderr, "zkbr_import_check: %s\n", e.what());
+        return -1;
+    }
+}
+
+/* the first zkb_libsnark_prove of a process under a key it has never seen (caches dropped first): key import + upload +
+ * tuning + proof.  Returns zkb_libsnark_prove's result followed by libsnark_verify's (0 = proved and accepted);
+ * seconds[0] = the cold call, seconds[1] = a second (warm) call. */
+int zkbr_cold_prove(void *h, uint64_t seed, double *seconds)
+{
+    Bench *b = (Bench *)h;
+    Credential c(b->payloads, seed);
+    c.ctx.pk_size = b->issuer->ctx.pk_size;
+    c.ctx.pk = (unsigned char *)malloc(c.ctx.pk_size);
+    memcpy(c.ctx.pk, b->issuer->ctx.pk, c.ctx.pk_size);
+    c.ctx.vk_size = b->issuer->ctx.vk_size;
+    c.ctx.vk = (unsigned char *)malloc(c.ctx.vk_size);
+    memcpy(c.ctx.vk, b->issuer->ctx.vk, c.ctx.vk_size);
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        g_keys_by_id.clear();
+    }
+    Session::get().clear(); /* device keys, contexts and the buffer identities: as in a fresh process */
+    double t = now_s();
+    int rc = zkb_libsnark_prove(&c.ctx);
+    seconds[0] = now_s() - t;
+    if (rc) return rc;
+    rc = libsnark_verify(&c.ctx);
+    if (rc) return 10 + rc;
+    free(c.ctx.proof);
+    c.ctx.proof = NULL;
+    t = now_s();
+    rc = zkb_libsnark_prove(&c.ctx);
+    seconds[1] = now_s() - t;
+    /* the Bench object's cached key set died with the session: re-create it for later calls on this handle */
+    b->key = key_for_ctx(&b->issuer->ctx);
+    return rc;
 }
 
 /* A `payloads`-payload credential end to end on a GPU-made key: zkb_libsnark_trusted_setup, then a proof by the

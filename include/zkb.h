@@ -93,6 +93,19 @@ int zkb_group_scalar_mul(zkb_ctx *ctx, int group, const uint64_t *scalars, const
  * every rank computes zkb_msm on its range, the 96- / 192-byte partials are gathered, one rank sums them. */
 int zkb_group_sum(zkb_ctx *ctx, int group, const uint64_t *points, size_t n, uint64_t *out);
 
+/* ---- key import: point decompression ---------------------------------------------
+ * libsnark stores a key element as (is_zero, X, least significant bit of Y) and recomputes Y = sqrt(X^3 + b) on import
+ * with one Tonelli-Shanks root per point (operator>>, libff/algebra/curves/alt_bn128/alt_bn128_g1.cpp:420-465,
+ * alt_bn128_g2.cpp:433-478; roots: libff/algebra/fields/fp.tcc:724-776, fp2.tcc:146-198) -- 7 s for the zklaim key,
+ * reached from libsnark_import_pk (zklaim/libsnark_wrapper.cpp:160-168, called by every libsnark_prove, :228-230).
+ * Here: n abscissas in, n affine points out.  x: n x 4 limbs (G1) / n x 8 limbs (G2: c0, c1), Montgomery; flags[i]:
+ * bit 0 = the stored lsb of Y (G2: of Y.c0) as a plain integer, bit 1 = is_zero (output: all-zero limbs); out_affine:
+ * n x 8 / n x 16 limbs.  status (optional, n entries): 1 = ok, 0 = X^3 + b is not a square.  Returns ZKB_ERR_ARG if
+ * any point failed.  (When Y.c0 == 0 in G2 both roots have the stored parity and the reference keeps whichever its
+ * root algorithm returns; that case has probability 2^-254 for a key element and is not distinguished here.) */
+int zkb_points_decompress(zkb_ctx *ctx, int group, const uint64_t *x, const uint8_t *flags, size_t n, uint64_t *out_affine,
+                          int32_t *status);
+
 /* ---- K4/K5: multi-scalar multiplication ------------------------------------------- */
 /* Uploads n affine bases and (precompute_factor > 1) their 2^(j*G*c) multiples so that up
  * to `precompute_factor` windows share one bucket set (HBM for doublings; B200 has 180 GB).
@@ -147,6 +160,8 @@ typedef struct {
     const uint64_t *L_query;  /* (num_variables - num_inputs) x 8 */
 } zkb_key_desc;
 
+/* All query / key-element pointers NULL = "constraint system only": the key then serves zkb_witness_map (config #4:
+ * the witness map needs the R1CS and its domain, not the queries); zkb_prove* on it returns ZKB_ERR_ARG. */
 int zkb_key_upload(zkb_ctx *ctx, const zkb_key_desc *desc, zkb_key **out);
 void zkb_key_free(zkb_key *key);
 size_t zkb_key_device_bytes(const zkb_key *key);
@@ -158,6 +173,8 @@ size_t zkb_key_device_bytes(const zkb_key *key);
 int zkb_key_tune(zkb_ctx *ctx, zkb_key *key, const uint64_t *w);
 /* window bits currently planned for the A, B-in-G1, H + L and B-in-G2 queries */
 int zkb_key_windows(const zkb_key *key, int out[4]);
+/* num_variables of the key's constraint system = field elements per witness */
+int zkb_key_num_variables(const zkb_key *key, size_t *nv_out);
 /* domain chosen for this key (what r1cs_to_qap_witness_map would use, r1cs_to_qap.tcc:218) */
 int zkb_key_domain(const zkb_key *key, size_t *m_out, int *kind_out);
 
@@ -174,9 +191,11 @@ typedef struct {
 
 /* r1cs_gg_ppzksnark_prover (r1cs_gg_ppzksnark.tcc:390-505) with the blinding scalars r, s
  * (:418-419) supplied by the caller (Montgomery Fr).  H_out (optional, may be NULL)
- * receives coefficients_for_H, (m + 1) x 4 limbs.  Returns ZKB_ERR_UNSAT if the H
- * polynomial's top coefficients are non-zero, i.e. the witness does not satisfy the
- * system (the reference asserts this, :406-408). */
+ * receives coefficients_for_H, (m + 1) x 4 limbs.  Returns ZKB_ERR_UNSAT when the witness
+ * does not satisfy the system: the device checks <a,z> * <b,z> == <c,z> for every constraint
+ * (r1cs_constraint_system::is_satisfied, which the reference asserts, :406-408, and which
+ * zklaim's generate_proof tests on the host, snark.cpp:119-124); the proof of such a witness
+ * is returned as all-zero limbs. */
 int zkb_prove(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4],
               zkb_proof *out, uint64_t *H_out);
 
@@ -204,6 +223,11 @@ int zkb_prove_combine(zkb_ctx *ctx, const zkb_partial *parts, size_t n, const ui
 int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r,
                     const uint64_t *s, zkb_proof *out);
 
+/* Per-proof outcome of the most recent zkb_prove / zkb_prove_batch* / zkb_prove_batch_collect call on this context:
+ * status[i] = ZKB_OK or ZKB_ERR_UNSAT (that call returned ZKB_ERR_UNSAT if any proof's witness was unsatisfying; the
+ * other proofs of the batch are valid, the offending ones are all-zero limbs). */
+int zkb_prove_batch_status(const zkb_ctx *ctx, int32_t *status, size_t n);
+
 /* Same with w (count x num_variables x 4 limbs), r and s (count x 4 limbs) already in device memory
  * on the context's device; the proofs still come back to the host (384 bytes each). */
 int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const void *d_w, const void *d_r,
@@ -218,6 +242,42 @@ int zkb_prove_batch_device(zkb_ctx *ctx, const zkb_key *key, size_t count, const
 int zkb_prove_batch_submit(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r,
                            const uint64_t *s);
 int zkb_prove_batch_collect(zkb_ctx *ctx, zkb_proof *out);
+
+/* ---- several GPUs from one host process -------------------------------------------------
+ * A pool owns one zkb_ctx per device and drives them with one host thread per device; a C caller shaped like
+ * zklaim/main_benchmark.c:174-198 (credential after credential through the prover) uses every GPU of the box
+ * through these calls without Python or NCCL.  zkb_pool_init(NULL, 0, ..) takes all visible devices.
+ *   zkb_pool_prove_batch     independent proofs: the batch is cut into one contiguous slice per device (key replicated
+ *                            by zkb_pool_key_upload); results in submission order;
+ *   zkb_pool_msm             one MSM, bases range-sharded the way libff::multi_exp chunks them (multiexp.tcc:417-431):
+ *                            device i holds and sums chunk i, the 96- / 192-byte partials are added on device 0
+ *                            (multiexp.tcc:433-438);
+ *   zkb_pool_prove_sharded   ONE proof over all devices (key set from zkb_pool_key_upload_sharded): zkb_prove_partial
+ *                            per device, zkb_prove_combine on device 0.
+ * Errors: the code of the first failing device; zkb_pool_last_error names it. */
+typedef struct zkb_pool zkb_pool;
+typedef struct zkb_key_set zkb_key_set;
+typedef struct zkb_bases_set zkb_bases_set;
+int zkb_device_count(void);
+int zkb_pool_init(const int *device_ids, int n, zkb_pool **out);
+void zkb_pool_shutdown(zkb_pool *pool);
+int zkb_pool_size(const zkb_pool *pool);
+zkb_ctx *zkb_pool_ctx(zkb_pool *pool, int i); /* the context of device i, e.g. for zkb_last_device_ms */
+const char *zkb_pool_last_error(const zkb_pool *pool);
+int zkb_pool_key_upload(zkb_pool *pool, const zkb_key_desc *desc, zkb_key_set **out);
+int zkb_pool_key_upload_sharded(zkb_pool *pool, const zkb_key_desc *desc, zkb_key_set **out);
+int zkb_pool_key_tune(zkb_pool *pool, zkb_key_set *keys, const uint64_t *w);
+const zkb_key *zkb_pool_key(const zkb_key_set *keys, int i);
+void zkb_pool_key_free(zkb_key_set *keys);
+/* status (optional, count entries): per-proof outcome as zkb_prove_batch_status reports it */
+int zkb_pool_prove_batch(zkb_pool *pool, const zkb_key_set *keys, size_t count, const uint64_t *w, const uint64_t *r,
+                         const uint64_t *s, zkb_proof *out, int32_t *status);
+int zkb_pool_prove_sharded(zkb_pool *pool, const zkb_key_set *keys, const uint64_t *w, const uint64_t r[4], const uint64_t s[4],
+                           zkb_proof *out);
+int zkb_pool_bases_upload(zkb_pool *pool, int group, const uint64_t *affine, size_t n, int window_bits, int precompute_factor,
+                          zkb_bases_set **out);
+void zkb_pool_bases_free(zkb_bases_set *bases);
+int zkb_pool_msm(zkb_pool *pool, const zkb_bases_set *bases, const uint64_t *scalars, size_t n, uint64_t *out);
 
 /* ---- the generator ---------------------------------------------------------------
  * r1cs_gg_ppzksnark_generator (r1cs_gg_ppzksnark.tcc:211-388) with its secret randomness supplied by the caller,

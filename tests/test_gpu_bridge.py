@@ -70,3 +70,30 @@ def test_batch_verification_through_the_zklaim_entry_point(cred):
     agree, accepted, _, _ = cred.verify_roundtrip(1, seed0=9100)
     assert (agree, accepted) == (1, 1)
     print(f"\nverify 16 credentials: reference libsnark_verify {t_ref * 1e3:.1f} ms, zkb_libsnark_verify_batch {t_gpu * 1e3:.1f} ms")
+
+
+def test_one_unsatisfied_credential_does_not_fail_the_batch(cred):
+    """zkb_libsnark_prove_batch_ex: per-credential results as libsnark_prove would give them (libsnark_wrapper.cpp:233-240):
+    the tampered credential gets 1 and no proof, the others get proofs the reference verifier accepts."""
+    good, rc = cred.batch_with_tampered(7, 4400, 2)
+    assert (good, rc) == (7, 1)
+    good, rc = cred.batch_with_tampered(3, 4500, 99)  # nobody tampered
+    assert (good, rc) == (3, 0)
+
+
+def test_deferred_key_import_equals_the_reference_importer(cred):
+    """libsnark_import_pk (square root per point on the host, libsnark_wrapper.cpp:160-168) and the
+    deferred importer (libsnark's framing, roots by zkb_points_decompress) give the same flat key, element for element"""
+    rc, t_ref, t_gpu = cred.import_check()
+    assert rc == 0
+    print(f"\nkey import: reference {t_ref:.2f} s, deferred (GPU roots) {t_gpu:.3f} s")
+    assert t_gpu < t_ref
+
+
+def test_cold_prove_on_a_new_key(cred):
+    """the first zkb_libsnark_prove of a process under a key it has never seen: import + upload + tuning + proof"""
+    rc, cold, warm = cred.cold_prove(31)
+    assert rc == 0
+    print(f"\ncold zkb_libsnark_prove {cold:.3f} s, warm {warm * 1e3:.1f} ms")
+    ok, _, _ = cred.roundtrip(2, 4600)  # the rebuilt session serves later calls
+    assert ok == 2

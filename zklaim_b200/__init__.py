@@ -44,6 +44,7 @@ SYMBOLS = {
     "zkb_group_op": (_i, [_vp, _i, _i, _u64p, _u64p, _u64p, _sz]),
     "zkb_group_scalar_mul": (_i, [_vp, _i, _u64p, _u64p, _u64p, _sz]),
     "zkb_group_sum": (_i, [_vp, _i, _u64p, _sz, _u64p]),
+    "zkb_points_decompress": (_i, [_vp, _i, _u64p, _vp, _sz, _u64p, _vp]),
     "zkb_bases_upload": (_i, [_vp, _i, _u64p, _sz, _i, _i, C.POINTER(_vp)]),
     "zkb_bases_free": (None, [_vp]),
     "zkb_bases_device_bytes": (_sz, [_vp]),
@@ -55,6 +56,24 @@ SYMBOLS = {
     "zkb_key_free": (None, [_vp]),
     "zkb_key_device_bytes": (_sz, [_vp]),
     "zkb_key_domain": (_i, [_vp, C.POINTER(_sz), C.POINTER(_i)]),
+    "zkb_key_num_variables": (_i, [_vp, C.POINTER(_sz)]),
+    "zkb_device_count": (_i, []),
+    "zkb_pool_init": (_i, [_vp, _i, C.POINTER(_vp)]),
+    "zkb_pool_shutdown": (None, [_vp]),
+    "zkb_pool_size": (_i, [_vp]),
+    "zkb_pool_ctx": (_vp, [_vp, _i]),
+    "zkb_pool_last_error": (C.c_char_p, [_vp]),
+    "zkb_pool_key_upload": (_i, [_vp, _vp, C.POINTER(_vp)]),
+    "zkb_pool_key_upload_sharded": (_i, [_vp, _vp, C.POINTER(_vp)]),
+    "zkb_pool_key_tune": (_i, [_vp, _vp, _u64p]),
+    "zkb_pool_key": (_vp, [_vp, _i]),
+    "zkb_pool_key_free": (None, [_vp]),
+    "zkb_pool_prove_batch": (_i, [_vp, _vp, _sz, _u64p, _u64p, _u64p, _vp, _vp]),
+    "zkb_prove_batch_status": (_i, [_vp, _vp, _sz]),
+    "zkb_pool_prove_sharded": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _vp]),
+    "zkb_pool_bases_upload": (_i, [_vp, _i, _u64p, _sz, _i, _i, C.POINTER(_vp)]),
+    "zkb_pool_bases_free": (None, [_vp]),
+    "zkb_pool_msm": (_i, [_vp, _vp, _u64p, _sz, _u64p]),
     "zkb_key_upload_shard": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
     "zkb_prove_partial": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _u64p, _u64p]),
     "zkb_prove_combine": (_i, [_vp, _u64p, _sz, _u64p, _u64p, _vp]),
@@ -152,6 +171,31 @@ class _SetupOut(C.Structure):
     _fields_ = [(f, C.c_void_p) for f in _SETUP_OUT]
 
 
+def _key_desc(key: dict):
+    """zkb_key_desc over the numpy arrays of `key`; returns (desc, the arrays it points into)"""
+    keep = []
+
+    def ptr(a, dtype=np.uint64):
+        a = np.ascontiguousarray(a, dtype=dtype)
+        keep.append(a)
+        return a.ctypes.data
+
+    d = _KeyDesc()
+    d.num_constraints, d.num_variables, d.num_inputs = key["num_constraints"], key["num_variables"], key["num_inputs"]
+    for name in "ABC":
+        rp, col, co = key["csr_" + name]
+        setattr(d, name, _CSR(ptr(rp), ptr(col, np.uint32), ptr(co)))
+    if "A_query" in key:
+        for f in ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "delta_g2", "A_query", "B_g1", "B_g2", "H_query",
+                  "L_query"):
+            setattr(d, f, ptr(key[f]))
+        d.B_index = ptr(key["B_index"], np.uint32)
+        d.B_nnz = len(key["B_index"])
+        d.H_size = len(key["H_query"])
+    # else: constraint system only (all query pointers NULL): the key serves witness_map alone
+    return d, keep
+
+
 class Proof(C.Structure):
     _fields_ = [("A", C.c_uint64 * 12), ("B", C.c_uint64 * 24), ("C", C.c_uint64 * 12)]
 
@@ -240,6 +284,20 @@ class Context:
         self._chk(self.lib.zkb_group_sum(self.h, group, p.ctypes.data, p.size // w, out.ctypes.data))
         return out
 
+    def points_decompress(self, group: int, x, flags):
+        """y = +-sqrt(x^3 + b) with the reference's parity rule (alt_bn128_g1.cpp:436-450, alt_bn128_g2.cpp:449-463).
+        x: n x 4 (G1) / n x 8 (G2) limbs; flags: n bytes, bit 0 = lsb of Y, bit 1 = is_zero.
+        Returns (affine points n x 8 / n x 16, status n: 1 = ok, 0 = x is not on the curve); raises on a bad x."""
+        w = 4 if group == G1 else 8
+        xa = _arr(x, w)
+        n = xa.size // w
+        fl = np.ascontiguousarray(flags, dtype=np.uint8)
+        assert fl.size == n
+        out = np.zeros((n, 2 * w), dtype=np.uint64)
+        st = np.zeros(n, dtype=np.int32)
+        self._chk(self.lib.zkb_points_decompress(self.h, group, xa.ctypes.data, fl.ctypes.data, n, out.ctypes.data, st.ctypes.data))
+        return out, st
+
     def upload_bases(self, group: int, affine, window_bits: int = 0, precompute_factor: int = 0) -> "Bases":
         w = 8 if group == G1 else 16
         a = _arr(affine, w)
@@ -268,25 +326,9 @@ class Context:
     # ---- key / prover -----------------------------------------------------------------
     def upload_key(self, key: dict, rank: int = 0, world: int = 1) -> "Key":
         """key: dict with the fields of zkb_key_desc as numpy arrays (bridge: zkb_libsnark.hpp flattens a libsnark proving key
-        into them).  world > 1: only shard `rank`'s range of every query goes to the device (zkb_key_upload_shard)."""
-        keep = []
-
-        def ptr(a, dtype=np.uint64):
-            a = np.ascontiguousarray(a, dtype=dtype)
-            keep.append(a)
-            return a.ctypes.data
-
-        d = _KeyDesc()
-        d.num_constraints, d.num_variables, d.num_inputs = key["num_constraints"], key["num_variables"], key["num_inputs"]
-        for name in "ABC":
-            rp, col, co = key["csr_" + name]
-            setattr(d, name, _CSR(ptr(rp), ptr(col, np.uint32), ptr(co)))
-        for f in ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "delta_g2", "A_query", "B_g1", "B_g2", "H_query",
-                  "L_query"):
-            setattr(d, f, ptr(key[f]))
-        d.B_index = ptr(key["B_index"], np.uint32)
-        d.B_nnz = len(key["B_index"])
-        d.H_size = len(key["H_query"])
+        into them).  world > 1: only shard `rank`'s range of every query goes to the device (zkb_key_upload_shard).
+        A dict without the query arrays uploads the constraint system only (witness_map)."""
+        d, keep = _key_desc(key)
         h = C.c_void_p()
         self._chk(self.lib.zkb_key_upload_shard(self.h, C.byref(d), rank, world, C.byref(h)))
         return Key(self, h, key["num_variables"])
@@ -502,6 +544,86 @@ class Key:
         if self.h:
             self.ctx.lib.zkb_key_free(self.h)
             self.h = None
+
+
+class Pool:
+    """zkb_pool: one context per device, one host thread per device (include/zkb.h).  devices=None: every visible GPU;
+    a device may be listed more than once (several contexts on one GPU: how the 1-GPU test tier exercises this path)."""
+
+    def __init__(self, devices=None):
+        self.lib = load_library()
+        ids = (C.c_int * len(devices))(*devices) if devices else None
+        h = C.c_void_p()
+        rc = self.lib.zkb_pool_init(ids, len(devices) if devices else 0, C.byref(h))
+        if rc != OK:
+            raise ZkbError(rc, (self.lib.zkb_last_error(None) or b"").decode())
+        self.h = h
+        self.size = int(self.lib.zkb_pool_size(self.h))
+
+    def _chk(self, rc: int):
+        if rc != OK:
+            raise ZkbError(rc, (self.lib.zkb_pool_last_error(self.h) or b"").decode())
+
+    def ctx(self, i: int) -> Context:
+        return Context.from_handle(self.lib.zkb_pool_ctx(self.h, i))
+
+    def upload_key(self, key: dict, sharded: bool = False):
+        d, keep = _key_desc(key)
+        h = C.c_void_p()
+        fn = self.lib.zkb_pool_key_upload_sharded if sharded else self.lib.zkb_pool_key_upload
+        self._chk(fn(self.h, C.byref(d), C.byref(h)))
+        return h
+
+    def tune_key(self, keys, w):
+        w = _arr(w, 4)
+        self._chk(self.lib.zkb_pool_key_tune(self.h, keys, w.ctypes.data))
+
+    def free_key(self, keys):
+        self.lib.zkb_pool_key_free(keys)
+
+    def prove_batch(self, keys, w, r, s):
+        """returns (proofs count x 48, status count: 0 or ERR_UNSAT); raises on any error but ERR_UNSAT"""
+        w, r, s = _arr(w, 4), _arr(r, 4), _arr(s, 4)
+        count = r.shape[0]
+        assert w.shape[0] == count and s.shape[0] == count
+        out = (Proof * count)()
+        st = np.zeros(count, dtype=np.int32)
+        rc = self.lib.zkb_pool_prove_batch(self.h, keys, count, w.ctypes.data, r.ctypes.data, s.ctypes.data, out, st.ctypes.data)
+        if rc not in (OK, ERR_UNSAT):
+            self._chk(rc)
+        return np.frombuffer(out, dtype=np.uint64).reshape(count, 48).copy(), st
+
+    def prove_sharded(self, keys, w, r, s) -> np.ndarray:
+        w, r, s = _arr(w, 4), _arr(r, 4), _arr(s, 4)
+        pr = Proof()
+        self._chk(self.lib.zkb_pool_prove_sharded(self.h, keys, w.ctypes.data, r.ctypes.data, s.ctypes.data, C.byref(pr)))
+        return pr.as_array()
+
+    def upload_bases(self, group: int, affine, window_bits: int = 0, precompute_factor: int = 0):
+        w = 8 if group == G1 else 16
+        a = _arr(affine, w)
+        h = C.c_void_p()
+        self._chk(self.lib.zkb_pool_bases_upload(self.h, group, a.ctypes.data, a.size // w, window_bits, precompute_factor, C.byref(h)))
+        return h, group
+
+    def msm(self, bases, scalars) -> np.ndarray:
+        h, group = bases
+        s = _arr(scalars, 4)
+        out = np.zeros(12 if group == G1 else 24, dtype=np.uint64)
+        self._chk(self.lib.zkb_pool_msm(self.h, h, s.ctypes.data, s.size // 4, out.ctypes.data))
+        return out
+
+    def free_bases(self, bases):
+        self.lib.zkb_pool_bases_free(bases[0])
+
+    def close(self):
+        if self.h:
+            self.lib.zkb_pool_shutdown(self.h)
+            self.h = None
+
+
+def device_count() -> int:
+    return int(load_library().zkb_device_count())
 
 
 def domain_select(min_size: int):

@@ -32,6 +32,10 @@ _SIG = {
     "zkbr_roundtrip": (_i, [_vp, _sz, _u64, _vp]),
     "zkbr_prove_tampered": (_i, [_vp, _u64]),
     "zkbr_setup_roundtrip": (_i, [_sz, _u64, _i, _vp]),
+    "zkbr_import_check": (_i, [_vp, _vp]),
+    "zkbr_batch_with_tampered": (_i, [_vp, _sz, _u64, _sz, C.POINTER(_i)]),
+    "zkbr_cold_prove": (_i, [_vp, _u64, _vp]),
+    "zkb_libsnark_devices": (_i, []),
 }
 _lib = None
 
@@ -108,6 +112,29 @@ class Credentials:
     def prove_tampered(self, seed: int = 77) -> int:
         """zkb_libsnark_prove on a credential whose hash was tampered with: the reference's contract says 1"""
         return int(self.L.zkbr_prove_tampered(self.h, seed))
+
+    def batch_with_tampered(self, count: int, seed0: int, tamper: int):
+        """count credentials, credential `tamper` with a flipped hash byte, through zkb_libsnark_prove_batch_ex.
+        Returns (credentials that behaved as the reference's libsnark_prove / libsnark_verify would, the call's result)"""
+        rc = C.c_int(0)
+        good = int(self.L.zkbr_batch_with_tampered(self.h, count, seed0, tamper, C.byref(rc)))
+        return good, rc.value
+
+    def import_check(self):
+        """the issuer's serialised proving key through the reference importer and through the deferred (GPU) importer.
+        Returns (0 if the flat keys are identical, reference import s, deferred import s)"""
+        t = (C.c_double * 2)()
+        rc = int(self.L.zkbr_import_check(self.h, t))
+        return rc, t[0], t[1]
+
+    def cold_prove(self, seed: int = 31):
+        """first zkb_libsnark_prove under a never-seen key (caches dropped).  NOTE: invalidates self.ctx / self.key
+        (the session is rebuilt); returns (rc, cold s, warm s)"""
+        t = (C.c_double * 2)()
+        rc = int(self.L.zkbr_cold_prove(self.h, seed, t))
+        self.ctx = Context.from_handle(self.L.zkbr_ctx())
+        self.key = Key(self.ctx, C.c_void_p(self.L.zkbr_key(self.h)), self.num_variables)
+        return rc, t[0], t[1]
 
     def close(self):
         if self.h:

@@ -57,6 +57,7 @@ struct zkb_ctx {
     size_t in_count[2] = {0, 0};
     int in_head = 0, in_pending = 0;
     std::vector<uint64_t> vf_abc_host; // verify.cu: the gamma_ABC_g1 array whose window table is resident (SV_TAB)
+    std::vector<int32_t> batch_status; // per proof of the most recent zkb_prove* call: 0 = ok, ZKB_ERR_UNSAT
     std::string err;
     double last_ms = 0.0;
     long launches = 0;

@@ -108,6 +108,100 @@ int stage(zkb_ctx *ctx, int slot, const void *host, size_t bytes, void **dev)
     *dev = ctx->scratch[slot].p;
     return ZKB_OK;
 }
+
+// ---- f1: point decompression (alt_bn128_g1.cpp:436-450, alt_bn128_g2.cpp:449-463) ---------------------------------
+// The reference stores a key element as (is_zero, X, lsb of Y) and recovers Y = sqrt(X^3 + b) with Tonelli-Shanks
+// (fp.tcc:724-776, fp2.tcc:146-198) on import, then picks the root whose plain-integer least significant bit (G2: of
+// Y.c0) equals the stored one.  q = 3 (mod 4), so a square root in Fq is the single fixed-exponent power
+// a^((q + 1) / 4); which root the algorithm returns does not matter, the parity rule selects the same Y.
+__device__ __forceinline__ Fq fq_sqrt_candidate(const Fq &a)
+{
+    uint32_t e[8]; // (q + 1) / 4: q + 1 does not carry out of the lowest word
+#pragma unroll
+    for (int i = 0; i < 8; i++) e[i] = FqP::P(i);
+    e[0] += 1u;
+#pragma unroll
+    for (int i = 0; i < 8; i++) e[i] = (e[i] >> 2) | (i < 7 ? (e[i + 1] << 30) : 0u);
+    Fq r = Fq::one();
+    for (int i = 253; i >= 0; i--) { // (q + 1) / 4 < 2^252
+        r = r.sqr();
+        if ((e[i >> 5] >> (i & 31)) & 1) r = r * a;
+    }
+    return r;
+}
+__device__ __forceinline__ bool fq_sqrt(const Fq &a, Fq &r)
+{
+    r = fq_sqrt_candidate(a);
+    return r.sqr() == a;
+}
+// square root in Fq2 = Fq[u] / (u^2 + 1) by the norm: a0 + a1 u = (x0 + x1 u)^2 with x0^2 = (a0 +- sqrt(a0^2 + a1^2)) / 2
+__device__ __forceinline__ bool fq2_sqrt(const Fq2 &a, const Fq &inv2, Fq2 &r)
+{
+    if (a.c1.is_zero()) {
+        Fq t;
+        if (fq_sqrt(a.c0, t)) {
+            r = Fq2{t, Fq::zero()};
+            return true;
+        }
+        if (!fq_sqrt(a.c0.neg(), t)) return false;
+        r = Fq2{Fq::zero(), t};
+        return true;
+    }
+    Fq s;
+    if (!fq_sqrt(a.c0.sqr() + a.c1.sqr(), s)) return false;
+    Fq x0;
+    if (!fq_sqrt((a.c0 + s) * inv2, x0) && !fq_sqrt((a.c0 - s) * inv2, x0)) return false;
+    r = Fq2{x0, a.c1 * x0.dbl().inverse()};
+    return r.sqr() == a;
+}
+__device__ __forceinline__ uint32_t plain_lsb(const Fq &y) { return y.from_mont().v[0] & 1u; }
+__device__ __forceinline__ uint32_t plain_lsb(const Fq2 &y) { return y.c0.from_mont().v[0] & 1u; }
+
+// flags[i]: bit 0 = the stored lsb of Y, bit 1 = is_zero.  status[i] = 1 ok, 0 = X is not the abscissa of a curve point
+__global__ void k_decompress_g1(const Fq *__restrict__ x, const uint8_t *__restrict__ flags, size_t n, Fq b,
+                                Affine<Fq> *__restrict__ out, int32_t *__restrict__ status)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Affine<Fq> p;
+    p.x = Fq::zero();
+    p.y = Fq::zero();
+    int ok = 1;
+    if (!(flags[i] & 2)) {
+        const Fq X = ld_vec(x + i);
+        Fq Y;
+        ok = fq_sqrt(X.sqr() * X + b, Y) ? 1 : 0;
+        if (ok) {
+            if (plain_lsb(Y) != (uint32_t)(flags[i] & 1)) Y = Y.neg();
+            p.x = X;
+            p.y = Y;
+        }
+    }
+    st_vec(out + i, p);
+    status[i] = ok;
+}
+__global__ void k_decompress_g2(const Fq2 *__restrict__ x, const uint8_t *__restrict__ flags, size_t n, Fq2 b, Fq inv2,
+                                Affine<Fq2> *__restrict__ out, int32_t *__restrict__ status)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Affine<Fq2> p;
+    p.x = Fq2::zero();
+    p.y = Fq2::zero();
+    int ok = 1;
+    if (!(flags[i] & 2)) {
+        const Fq2 X = ld_vec(x + i);
+        Fq2 Y;
+        ok = fq2_sqrt(X.sqr() * X + b, inv2, Y) ? 1 : 0;
+        if (ok) {
+            if (plain_lsb(Y) != (uint32_t)(flags[i] & 1)) Y = Y.neg();
+            p.x = X;
+            p.y = Y;
+        }
+    }
+    st_vec(out + i, p);
+    status[i] = ok;
+}
 } // namespace
 
 extern "C" {
@@ -208,6 +302,53 @@ int zkb_group_scalar_mul(zkb_ctx *ctx, int group, const uint64_t *scalars, const
     ZKB_LAUNCH_CHECK(ctx);
     ZKB_CUDA(ctx, cudaMemcpyAsync(out, d_o, n * es, cudaMemcpyDeviceToHost, ctx->stream));
     ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ZKB_OK;
+}
+
+
+int zkb_points_decompress(zkb_ctx *ctx, int group, const uint64_t *x, const uint8_t *flags, size_t n, uint64_t *out_affine,
+                          int32_t *status)
+{
+    if (!ctx || !x || !flags || !out_affine || (group != ZKB_G1 && group != ZKB_G2))
+        return fail(ctx, ZKB_ERR_ARG, "zkb_points_decompress: bad argument");
+    if (n == 0) return ZKB_OK;
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    const size_t xs = group == ZKB_G1 ? 32 : 64, ps = 2 * xs;
+    void *dx, *df;
+    int rc;
+    if ((rc = stage(ctx, SB_A, x, n * xs, &dx))) return rc;
+    if ((rc = stage(ctx, SB_B, flags, n, &df))) return rc;
+    ZKB_CUDA(ctx, ctx->scratch[SB_O].ensure(n * ps + n * 4));
+    char *d_o = ctx->scratch[SB_O].as<char>();
+    int32_t *d_st = (int32_t *)(d_o + n * ps);
+    // curve coefficients (alt_bn128_init.cpp:124-128): b = 3, twist b = 3 / (9 + u); host side of fp.cuh
+    Fq three = Fq::zero();
+    three.v[0] = 3;
+    three = three.to_mont();
+    const unsigned g = ceil_div(n, 64);
+    if (group == ZKB_G1) {
+        k_decompress_g1<<<g, 64, 0, ctx->stream>>>((const Fq *)dx, (const uint8_t *)df, n, three, (Affine<Fq> *)d_o, d_st);
+    } else {
+        Fq nine = Fq::zero();
+        nine.v[0] = 9;
+        nine = nine.to_mont();
+        const Fq2 xi_inv = Fq2{nine, Fq::one()}.inverse();
+        const Fq2 twist_b = Fq2{three * xi_inv.c0, three * xi_inv.c1};
+        const Fq inv2 = Fq::one().dbl().inverse();
+        k_decompress_g2<<<g, 64, 0, ctx->stream>>>((const Fq2 *)dx, (const uint8_t *)df, n, twist_b, inv2, (Affine<Fq2> *)d_o, d_st);
+    }
+    ZKB_LAUNCH_CHECK(ctx);
+    ZKB_CUDA(ctx, cudaMemcpyAsync(out_affine, d_o, n * ps, cudaMemcpyDeviceToHost, ctx->stream));
+    std::vector<int32_t> st_host;
+    int32_t *st = status;
+    if (!st) {
+        st_host.resize(n);
+        st = st_host.data();
+    }
+    ZKB_CUDA(ctx, cudaMemcpyAsync(st, d_st, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < n; i++)
+        if (!st[i]) return fail(ctx, ZKB_ERR_ARG, "zkb_points_decompress: an abscissa is not on the curve");
     return ZKB_OK;
 }
 

@@ -30,7 +30,8 @@
 //
 // Layout in HBM: bases AoS affine (64 B G1 / 128 B G2 per point, 16-byte vector loads; a
 // gathered point is exactly two / four full 32-byte sectors), copies stored copy-major
-// [F][n]; buckets and partials XYZZ AoS (128 B / 256 B); the pair list is two u32 arrays.
+// [F][n]; buckets and partials XYZZ AoS (128 B / 256 B); the sorted pair list is one u32 array (point index | sign)
+// plus the bucket boundaries start[B + 1].
 #include "msm_impl.cuh"
 #include <string.h>
 
@@ -112,8 +113,7 @@ __global__ void k_count(JobTab tab, const uint32_t *__restrict__ sidx, const uin
 }
 
 __global__ void k_scatter(JobTab tab, const uint32_t *__restrict__ sidx, const uint32_t *__restrict__ plain,
-                          size_t zstride, uint32_t *__restrict__ cursor, uint32_t *__restrict__ ent,
-                          uint32_t *__restrict__ ebkt)
+                          size_t zstride, uint32_t *__restrict__ cursor, uint32_t *__restrict__ ent)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t p = blockIdx.y;
@@ -131,8 +131,106 @@ __global__ void k_scatter(JobTab tab, const uint32_t *__restrict__ sidx, const u
         const uint32_t pos = atomicAdd(&cursor[b], 1u);
         const uint32_t q = (uint32_t)(w / J.G);
         ent[pos] = (pt0 + q * J.n_total) | (d < 0 ? 0x80000000u : 0u);
-        ebkt[pos] = b;
     });
+}
+
+// ---- block-local form of the two kernels above (one proof's bucket space fits in shared memory) -------------
+// Block (j, p) owns the items [j * chunk, (j + 1) * chunk) of proof p.  It counts its pairs in a shared-memory
+// histogram of the proof's Bp buckets and writes the counts to hist[(p * NB + j) * Bp + b] (coalesced);
+// k_bucket_totals / the scan / k_block_cursors turn them into one write cursor per (block, bucket), which the
+// scatter pass loads back into shared memory: no global atomic is left in either pass.  Scalars equal to one --
+// nearly half of a Groth16 witness, all landing in ONE bucket -- are counted once per warp (ballot) instead of lane
+// by lane.  NB is chosen so that the proofs in flight at any time write a region of the sorted list that fits in L2
+// (4-byte scattered stores that miss L2 cost a DRAM read-modify-write each).
+constexpr int SORT_T = 256;
+__device__ __forceinline__ bool is_plain_one(const uint32_t *k)
+{
+    return k[0] == 1u && (k[1] | k[2] | k[3] | k[4] | k[5] | k[6] | k[7]) == 0u;
+}
+// `SCATTER` = false: count; true: place.  sh: Bp words (counts, or cursors).
+template <bool SCATTER>
+__global__ void __launch_bounds__(SORT_T)
+k_sort_local(JobTab tab, const uint32_t *__restrict__ sidx, const uint32_t *__restrict__ plain, size_t zstride, uint32_t chunk,
+             uint32_t *__restrict__ hist, uint32_t *__restrict__ ent)
+{
+    extern __shared__ uint32_t sh[];
+    const uint32_t p = blockIdx.y, j = blockIdx.x, NB = gridDim.x, Bp = tab.Bp;
+    uint32_t *g = hist + ((size_t)p * NB + j) * Bp;
+    for (uint32_t b = threadIdx.x; b < Bp; b += SORT_T) sh[b] = SCATTER ? g[b] : 0u;
+    __syncthreads();
+    const uint32_t lo = j * chunk, hi = min(lo + chunk, tab.n_items);
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint32_t i0 = lo; i0 < hi; i0 += SORT_T) { // chunk is a multiple of SORT_T: whole warps stay together
+        const uint32_t i = i0 + threadIdx.x;
+        int job = 0;
+        uint32_t li = 0, k[8];
+        const bool live = i < hi && load_item(tab, sidx, plain, zstride, i, p, job, li, k);
+        const MsmJob J = tab.j[job];
+        const uint32_t nb = 1u << (J.c - 1);
+        const uint32_t pt0 = J.pts_off + J.base_first + li;
+        const bool one = live && is_plain_one(k);
+        // scalar == 1: a single pair in bucket (window 0, digit 1) of the item's job; aggregated over the lanes that
+        // share the job
+        unsigned rem = __ballot_sync(0xffffffffu, one);
+        while (rem) { // one iteration per job present among the warp's ones (usually a single one)
+            const int leader = __ffs(rem) - 1;
+            const int lead_job = __shfl_sync(0xffffffffu, job, leader);
+            const unsigned grp = __ballot_sync(0xffffffffu, one && job == lead_job);
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(&sh[J.bucket_off], (uint32_t)__popc(grp));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (SCATTER && one && job == lead_job) {
+                const uint32_t pos = base + (uint32_t)__popc(grp & ((1u << lane) - 1u));
+                ent[pos] = pt0;
+            }
+            rem &= ~grp;
+        }
+        if (live && !one) {
+            for_each_digit(k, J.c, J.W, [&](int w, int d) {
+                const uint32_t mag = (uint32_t)(d < 0 ? -d : d);
+                const uint32_t b = J.bucket_off + (uint32_t)(w % J.G) * nb + (mag - 1);
+                const uint32_t pos = atomicAdd(&sh[b], 1u);
+                if (SCATTER) {
+                    const uint32_t q = (uint32_t)(w / J.G);
+                    ent[pos] = (pt0 + q * J.n_total) | (d < 0 ? 0x80000000u : 0u);
+                }
+            });
+        }
+    }
+    if (!SCATTER) {
+        __syncthreads();
+        for (uint32_t b = threadIdx.x; b < Bp; b += SORT_T) g[b] = sh[b];
+    }
+}
+
+// tot[p * Bp + b] = sum over the NB blocks of proof p of their count for bucket b
+__global__ void k_bucket_totals(const uint32_t *__restrict__ hist, uint32_t Bp, uint32_t NB, uint32_t *__restrict__ tot)
+{
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
+    if (b >= Bp) return;
+    const uint32_t *h = hist + (size_t)p * NB * Bp + b;
+    uint32_t s = 0;
+    for (uint32_t j = 0; j < NB; j++) s += h[(size_t)j * Bp];
+    tot[(size_t)p * Bp + b] = s;
+}
+// hist[p][j][b] <- start[p * Bp + b] + the counts of the blocks j' < j: the first position block j writes in bucket b.
+// Eight loads are issued before the first store, so the column walk is not one dependent memory round trip per block.
+__global__ void k_block_cursors(uint32_t *hist, uint32_t Bp, uint32_t NB, const uint32_t *__restrict__ start)
+{
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
+    if (b >= Bp) return;
+    uint32_t *h = hist + (size_t)p * NB * Bp + b;
+    uint32_t run = start[(size_t)p * Bp + b];
+    for (uint32_t j0 = 0; j0 < NB; j0 += 8) {
+        uint32_t c[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) c[u] = j0 + u < NB ? h[(size_t)(j0 + u) * Bp] : 0u;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            if (j0 + u < NB) h[(size_t)(j0 + u) * Bp] = run;
+            run += c[u];
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------
@@ -193,9 +291,9 @@ __global__ void k_scan_block_sums(uint32_t *__restrict__ block_sums, unsigned nb
     }
 }
 
-// out[i] = exclusive prefix; out[n] = total.  `out2` receives a second copy of out[0..n).
-__global__ void k_scan_final(const uint32_t *__restrict__ in, size_t n, const uint32_t *__restrict__ block_sums,
-                             uint32_t *__restrict__ out, uint32_t *__restrict__ out2)
+// start[i] = exclusive prefix of in[0..n), start[n] = total; `cursor` (optional, may alias in) receives a second copy
+__global__ void k_scan_final(const uint32_t *in, size_t n, const uint32_t *__restrict__ block_sums,
+                             uint32_t *cursor, uint32_t *__restrict__ start)
 {
     __shared__ uint32_t sm[32];
     size_t base = (size_t)blockIdx.x * SCAN_BLK + (size_t)threadIdx.x * SCAN_E;
@@ -211,11 +309,11 @@ __global__ void k_scan_final(const uint32_t *__restrict__ in, size_t n, const ui
 #pragma unroll
     for (int j = 0; j < SCAN_E; j++) {
         if (base + j < n) {
-            out[base + j] = e;
-            if (out2) out2[base + j] = e;
+            if (cursor) cursor[base + j] = e;
+            start[base + j] = e;
         }
         e += v[j];
-        if (base + j + 1 == n) out[n] = e;
+        if (base + j + 1 == n) start[n] = e;
     }
 }
 
@@ -294,6 +392,9 @@ void plan_free(MsmPlan *plan)
     plan->d_sidx = nullptr;
 }
 
+// shared-memory budget of the block-local sort: a proof's bucket space must fit (4 bytes per bucket)
+constexpr uint32_t SORT_LOCAL_MAX_BP = 49152;
+
 int msm_sort_pairs(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t *d_plain, size_t zstride,
                    int batch)
 {
@@ -301,34 +402,72 @@ int msm_sort_pairs(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const u
     const int gs = msm_slot(ctx, plan->group);
     size_t Emax = 0;
     for (uint32_t q = 0; q < tab.njobs; q++) Emax += (size_t)tab.j[q].n * tab.j[q].W;
+    const size_t e_proof = Emax;
     Emax *= (size_t)batch;
     const size_t B = (size_t)tab.Bp * batch;
     if (Emax >= (1ull << 32) || B >= (1ull << 32)) return fail(ctx, ZKB_ERR_ARG, "msm: more than 2^32 pairs in one run");
+    // block-local sort: NB blocks per proof.  About three blocks per SM are resident; the proofs in flight
+    // (resident / NB) should write no more than ~48 MB of the sorted list at a time; every block wants >= 1024 items.
+    const bool local = tab.Bp <= SORT_LOCAL_MAX_BP;
+    uint32_t NB = 1, chunk = 0;
+    if (local) {
+        const uint32_t resident = (uint32_t)ctx->sm_count * 3;
+        uint32_t want = (resident + (uint32_t)batch - 1) / (uint32_t)batch;              // fill the device
+        const size_t inflight_max = ((size_t)48 << 20) / (e_proof * 4 + 1) + 1;          // proofs whose output fits in L2
+        if ((size_t)resident / want > inflight_max) want = (uint32_t)((resident + inflight_max - 1) / inflight_max);
+        const uint32_t most = (tab.n_items + 1023) / 1024;
+        NB = want < most ? want : most;
+        if (NB < 1) NB = 1;
+        if (NB > 1024) NB = 1024;
+        chunk = ((tab.n_items + NB - 1) / NB + SORT_T - 1) / SORT_T * SORT_T;
+        NB = (tab.n_items + chunk - 1) / chunk;
+        if (B * NB >= (1ull << 32)) return fail(ctx, ZKB_ERR_ARG, "msm: bucket space too large");
+    }
     const unsigned scan_blocks = ceil_div(B, SCAN_BLK);
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_HIST].ensure(B * 4));
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_START].ensure((B + 1) * 4));
-    ZKB_CUDA(ctx, ctx->scratch[gs + SB_CURSOR].ensure(B * 4));
+    ZKB_CUDA(ctx, ctx->scratch[gs + SB_CURSOR].ensure(B * NB * 4));
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_BLOCKSUM].ensure((size_t)scan_blocks * 4 + 16));
     ZKB_CUDA(ctx, ctx->scratch[gs + SB_ENT].ensure(Emax * 4 + 16));
-    ZKB_CUDA(ctx, ctx->scratch[gs + SB_EBKT].ensure(Emax * 4 + 16));
-    uint32_t *hist = ctx->scratch[gs + SB_HIST].as<uint32_t>();
+    uint32_t *tot = ctx->scratch[gs + SB_HIST].as<uint32_t>();      // pairs per bucket
     uint32_t *start = ctx->scratch[gs + SB_START].as<uint32_t>();
-    uint32_t *cursor = ctx->scratch[gs + SB_CURSOR].as<uint32_t>();
+    uint32_t *cursor = ctx->scratch[gs + SB_CURSOR].as<uint32_t>(); // local: counts, then cursors, per (proof, block, bucket)
     uint32_t *bsum = ctx->scratch[gs + SB_BLOCKSUM].as<uint32_t>();
     uint32_t *ent = ctx->scratch[gs + SB_ENT].as<uint32_t>();
-    uint32_t *ebkt = ctx->scratch[gs + SB_EBKT].as<uint32_t>();
 
-    ZKB_CUDA(ctx, cudaMemsetAsync(hist, 0, B * 4, st));
-    const dim3 grid(ceil_div(tab.n_items, 128), (unsigned)batch);
-    k_count<<<grid, 128, 0, st>>>(tab, plan->d_sidx, d_plain, zstride, hist);
-    ZKB_LAUNCH_CHECK(ctx);
-    k_scan_sums<<<scan_blocks, SCAN_T, 0, st>>>(hist, B, bsum);
+    const size_t smem = (size_t)tab.Bp * 4;
+    const dim3 bgrid(ceil_div(tab.Bp, 256), (unsigned)batch);
+    if (local) {
+        const uint32_t attr_bit = 8u;
+        if (!(ctx->func_attr_done & attr_bit)) {
+            ZKB_CUDA(ctx, cudaFuncSetAttribute(k_sort_local<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SORT_LOCAL_MAX_BP * 4)));
+            ZKB_CUDA(ctx, cudaFuncSetAttribute(k_sort_local<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SORT_LOCAL_MAX_BP * 4)));
+            ctx->func_attr_done |= attr_bit;
+        }
+        k_sort_local<false><<<dim3(NB, (unsigned)batch), SORT_T, smem, st>>>(tab, plan->d_sidx, d_plain, zstride, chunk, cursor, nullptr);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_bucket_totals<<<bgrid, 256, 0, st>>>(cursor, tab.Bp, NB, tot);
+        ZKB_LAUNCH_CHECK(ctx);
+    } else {
+        ZKB_CUDA(ctx, cudaMemsetAsync(tot, 0, B * 4, st));
+        const dim3 grid(ceil_div(tab.n_items, 128), (unsigned)batch);
+        k_count<<<grid, 128, 0, st>>>(tab, plan->d_sidx, d_plain, zstride, tot);
+        ZKB_LAUNCH_CHECK(ctx);
+    }
+    k_scan_sums<<<scan_blocks, SCAN_T, 0, st>>>(tot, B, bsum);
     ZKB_LAUNCH_CHECK(ctx);
     k_scan_block_sums<<<1, SCAN_T, 0, st>>>(bsum, scan_blocks);
     ZKB_LAUNCH_CHECK(ctx);
-    k_scan_final<<<scan_blocks, SCAN_T, 0, st>>>(hist, B, bsum, start, cursor);
+    k_scan_final<<<scan_blocks, SCAN_T, 0, st>>>(tot, B, bsum, local ? nullptr : cursor, start);
     ZKB_LAUNCH_CHECK(ctx);
-    k_scatter<<<grid, 128, 0, st>>>(tab, plan->d_sidx, d_plain, zstride, cursor, ent, ebkt);
+    if (local) {
+        k_block_cursors<<<bgrid, 256, 0, st>>>(cursor, tab.Bp, NB, start);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_sort_local<true><<<dim3(NB, (unsigned)batch), SORT_T, smem, st>>>(tab, plan->d_sidx, d_plain, zstride, chunk, cursor, ent);
+    } else {
+        const dim3 grid(ceil_div(tab.n_items, 128), (unsigned)batch);
+        k_scatter<<<grid, 128, 0, st>>>(tab, plan->d_sidx, d_plain, zstride, cursor, ent);
+    }
     ZKB_LAUNCH_CHECK(ctx);
     return ZKB_OK;
 }
@@ -351,7 +490,7 @@ int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t
         const bool prof = ctx->prof && !ctx->prof_pending[g] && (g == 1 || ctx->lane_bias == 0); // one sample per synchronisation
         if (prof) ZKB_CUDA(ctx, cudaEventRecord(ctx->pe[g][0], ctx->stream));
         rc = launch_accumulate<F>(ctx, (const Affine<F> *)plan->d_pts, ctx->scratch[gs + SB_ENT].as<uint32_t>(),
-                                  ctx->scratch[gs + SB_EBKT].as<uint32_t>(), ctx->scratch[gs + SB_START].as<uint32_t>(),
+                                  ctx->scratch[gs + SB_START].as<uint32_t>(),
                                   (uint32_t)B, rmax, ctx->scratch[gs + SB_BUCKETS].as<PT>(), ctx->scratch[gs + SB_PARTS].as<PT>());
         if (rc) return rc;
         if (prof) {

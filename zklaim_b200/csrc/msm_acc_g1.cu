@@ -2,6 +2,6 @@
 // with the Montgomery multiplier fully inlined.
 #include "msm_acc_impl.cuh"
 namespace zkb {
-template int launch_accumulate<Fq>(zkb_ctx *, const Affine<Fq> *, const uint32_t *, const uint32_t *, const uint32_t *,
-                                   uint32_t, uint32_t, XYZZ<Fq> *, XYZZ<Fq> *);
+template int launch_accumulate<Fq>(zkb_ctx *, const Affine<Fq> *, const uint32_t *, const uint32_t *, uint32_t,
+                                   uint32_t, XYZZ<Fq> *, XYZZ<Fq> *);
 }

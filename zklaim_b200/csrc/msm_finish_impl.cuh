@@ -265,6 +265,68 @@ k_reduce_l2(const XYZZ<F> *__restrict__ l1, int NB, int logCH, XYZZ<F> *__restri
     }
 }
 
+// ---- the same weighted sum for large bucket sets, without a scan over the buckets -------------------------------
+// View the nb = H2 * W2 buckets of a set as a grid, b = hi * W2 + lo:
+//     sum_b (b + 1) E_b  =  W2 * sum_hi hi * Row_hi  +  sum_lo (lo + 1) * Col_lo,   Row_hi = sum_lo E, Col_lo = sum_hi E.
+// The row and column sums are plain sums: two additions per bucket with every lane busy and no shared memory
+// (k_reduce_rowcol: one thread per segment of a row or of a column); the two weighted sums that remain have H2 and
+// W2 terms only (k_reduce_rowcol_finish, one block per set).  The running-sum form (k_reduce_l1 / l2) costs about
+// 3.3 additions per bucket once its block-level scans are counted.
+template <class F>
+__global__ void __launch_bounds__(128)
+k_reduce_rowcol(const XYZZ<F> *__restrict__ buckets, uint32_t Bp, uint32_t bucket_off, uint32_t G, uint32_t nb, int lw, int lh,
+                int lseg, XYZZ<F> *__restrict__ part)
+{
+    const uint32_t set = blockIdx.y;
+    const size_t base = (size_t)(set / G) * Bp + bucket_off + (size_t)(set % G) * nb;
+    const uint32_t W2 = 1u << lw, H2 = 1u << lh;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t nrow = H2 << lseg, ncol = W2 << lseg;
+    if (t >= nrow + ncol) return;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    if (t < nrow) { // a segment of a row: consecutive buckets
+        const uint32_t len = W2 >> lseg;
+        const XYZZ<F> *E = buckets + base + (size_t)(t >> lseg) * W2 + (size_t)(t & ((1u << lseg) - 1u)) * len;
+        for (uint32_t u = 0; u < len; u++) acc.add(ld_vec(E + u));
+    } else { // a segment of a column: consecutive threads read consecutive buckets
+        const uint32_t u0 = t - nrow, col = u0 & (W2 - 1u), seg = u0 >> lw, len = H2 >> lseg;
+        const XYZZ<F> *E = buckets + base + (size_t)seg * len * W2 + col;
+        for (uint32_t u = 0; u < len; u++) acc.add(ld_vec(E + (size_t)u * W2));
+    }
+    st_vec(part + (size_t)set * (nrow + ncol) + t, acc);
+}
+
+// one block of 2 * H2 threads per set (H2 >= W2): the first half reduces the rows, the second half the columns, side
+// by side;  R_set = W2 * sum_{hi >= 1} suffix_hi(Row) + sum_lo suffix_lo(Col)
+template <class F>
+__global__ void __launch_bounds__(512)
+k_reduce_rowcol_finish(const XYZZ<F> *__restrict__ part, int lw, int lh, int lseg, XYZZ<F> *__restrict__ out)
+{
+    extern __shared__ uint32_t sm_all[];
+    const int T = blockDim.x >> 1, half = threadIdx.x >= T ? 1 : 0, t = threadIdx.x - half * T;
+    uint32_t *sm = sm_all + (size_t)half * T * (sizeof(XYZZ<F>) / 4);
+    const uint32_t set = blockIdx.x, W2 = 1u << lw, H2 = 1u << lh, SEG = 1u << lseg;
+    const XYZZ<F> *p = part + (size_t)set * ((H2 + W2) << lseg);
+    XYZZ<F> v = XYZZ<F>::inf();
+    if (!half) { // row t: its SEG segment sums are consecutive
+        for (uint32_t s = 0; s < SEG; s++) v.add(ld_vec(p + (size_t)t * SEG + s));
+    } else if ((uint32_t)t < W2) {
+        for (uint32_t s = 0; s < SEG; s++) v.add(ld_vec(p + (size_t)(H2 << lseg) + (size_t)s * W2 + t));
+    }
+    block_suffix_scan(sm, T, t, v);
+    if (!half && t == 0) v = XYZZ<F>::inf(); // rows carry the weight hi, columns lo + 1
+    block_sum(sm, T, t, v);
+    if (!half && t == 0) {
+        for (int i = 0; i < lw; i++) v = v.dbl();
+        sm_put(sm, T, 1, v);
+    }
+    __syncthreads();
+    if (half && t == 0) {
+        v.add(sm_get<XYZZ<F>>(sm_all, T, 1));
+        st_vec(out + set, v);
+    }
+}
+
 // Horner over the G bucket sets of every proof: res[p * njobs + job] = sum_g 2^(g*c) R_{p,g}
 template <class F>
 __global__ void k_final(const XYZZ<F> *__restrict__ sets, int batch, int G, int c, int njobs, int job,
@@ -347,6 +409,30 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
     for (uint32_t q = 0; q < tab.njobs; q++) {
         const MsmJob &J = tab.j[q];
         const uint32_t nb = 1u << (J.c - 1);
+        const size_t sets = (size_t)batch * J.G;
+        if (sets > 65535) return fail(ctx, ZKB_ERR_ARG, "msm: batch * bucket sets exceeds 65535");
+        ZKB_CUDA(ctx, ctx->scratch[gs + SB_L2].ensure(sets * sizeof(PT)));
+        PT *l2 = ctx->scratch[gs + SB_L2].as<PT>();
+        if (nb >= 1024 && nb <= 65536 && sets * nb >= (size_t)ctx->sm_count * 2048) {
+            // plenty of buckets (a batch): row / column sums over an H2 x W2 grid, segments per line so that about
+            // 512 threads per SM exist; few buckets (a single proof) are latency-bound and keep the scan form below
+            const int lw = (J.c - 1) / 2, lh = (J.c - 1) - lw;
+            int lseg = 0;
+            while (lseg < 4 && lseg < lw && (sets << (lh + 1 + lseg)) < (size_t)ctx->sm_count * 512) lseg++;
+            const size_t per_set = ((size_t)1 << (lh + lseg)) + ((size_t)1 << (lw + lseg));
+            ZKB_CUDA(ctx, ctx->scratch[gs + SB_L1].ensure(sets * per_set * sizeof(PT)));
+            PT *part = ctx->scratch[gs + SB_L1].as<PT>();
+            k_reduce_rowcol<F><<<dim3(ceil_div(per_set, 128), (unsigned)sets), 128, 0, st>>>(buckets, tab.Bp, J.bucket_off, J.G, nb, lw, lh, lseg, part);
+            ZKB_LAUNCH_CHECK(ctx);
+            const int T2 = 1 << lh; // lh >= lw
+            const uint32_t attr_bit = plan->group == ZKB_G2 ? 32u : 16u;
+            if (!(ctx->func_attr_done & attr_bit)) {
+                ZKB_CUDA(ctx, cudaFuncSetAttribute(k_reduce_rowcol_finish<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(512 * sizeof(PT))));
+                ctx->func_attr_done |= attr_bit;
+            }
+            k_reduce_rowcol_finish<F><<<(unsigned)sets, 2 * T2, (size_t)2 * T2 * sizeof(PT), st>>>(part, lw, lh, lseg, l2);
+            ZKB_LAUNCH_CHECK(ctx);
+        } else {
         // level-1 reduction geometry: nb = NB * T * L
         // buckets per thread: enough threads to fill the device when the batch is small (the serial chain is
         // 2 L + 2 log2 T additions deep), fewer scan steps per bucket when there is plenty of work
@@ -359,12 +445,8 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
         if (NB > 128) return fail(ctx, ZKB_ERR_ARG, "msm: window too wide for the bucket reduction");
         int T2 = 1;
         while (T2 < NB) T2 <<= 1;
-        const size_t sets = (size_t)batch * J.G;
-        if (sets > 65535) return fail(ctx, ZKB_ERR_ARG, "msm: batch * bucket sets exceeds 65535");
         ZKB_CUDA(ctx, ctx->scratch[gs + SB_L1].ensure(2 * sets * NB * sizeof(PT)));
-        ZKB_CUDA(ctx, ctx->scratch[gs + SB_L2].ensure(sets * sizeof(PT)));
         PT *l1 = ctx->scratch[gs + SB_L1].as<PT>();
-        PT *l2 = ctx->scratch[gs + SB_L2].as<PT>();
         int logL = 0;
         while ((1 << logL) < L) logL++;
         k_reduce_l1<F><<<dim3(NB, (unsigned)sets), T, (size_t)T * sizeof(PT), st>>>(buckets, tab.Bp, J.bucket_off, J.G, nb, L,
@@ -374,6 +456,7 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
         while ((1u << logCH) < (uint32_t)T * L) logCH++;
         k_reduce_l2<F><<<(unsigned)sets, T2, (size_t)T2 * sizeof(PT), st>>>(l1, NB, logCH, l2);
         ZKB_LAUNCH_CHECK(ctx);
+        }
         k_final<F><<<ceil_div((size_t)batch, 32), 32, 0, st>>>(l2, batch, J.G, J.c, (int)tab.njobs, (int)q, d_res);
         ZKB_LAUNCH_CHECK(ctx);
     }

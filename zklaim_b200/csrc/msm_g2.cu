@@ -5,7 +5,7 @@
 #include "msm_finish_impl.cuh"
 namespace zkb {
 template int launch_accumulate<Fq2>(zkb_ctx *, const Affine<Fq2> *, const uint32_t *, const uint32_t *,
-                                    const uint32_t *, uint32_t, uint32_t, XYZZ<Fq2> *, XYZZ<Fq2> *);
+                                    uint32_t, uint32_t, XYZZ<Fq2> *, XYZZ<Fq2> *);
 template int msm_finish<Fq2>(zkb_ctx *, const MsmPlan *, const JobTab &, int, uint32_t, XYZZ<Fq2> *);
 template int plan_upload_job<Fq2>(zkb_ctx *, MsmPlan *, int, const uint64_t *, bool);
 template int results_to_host<Fq2>(zkb_ctx *, const XYZZ<Fq2> *, size_t, uint64_t *);

@@ -21,14 +21,16 @@
 // Twiddles w^i, i < n/2 are tabulated once per domain in HBM (L2-resident for the sizes of
 // the zklaim circuit).
 #include "ntt.cuh"
+#include "ntt_tile.cuh"
+#include <stdlib.h>
 
 using namespace zkb;
 
 namespace {
 
 constexpr int NTT_T = 256;     // threads per block
-constexpr int NTT_KMAX = 8;    // butterfly levels per pass
 constexpr int NTT_EMAX = 2048; // elements staged per block (64 KB of shared memory)
+constexpr int NTT_TILE_DEFAULT = 11;
 #ifndef NTT_TFAST
 #define NTT_TFAST 1 // 1: lanes walk the t index in the staging loops (coalesced rows, but shared-memory stride C); 0: always the column index
 #endif
@@ -143,6 +145,24 @@ k_ntt_pass(Fr *__restrict__ data, size_t vstride, int L, int lobits, int k, int 
     }
 }
 
+// The register-radix pass (ntt_tile.cuh): eight elements per thread, two or three butterfly levels per round in
+// registers, one shared-memory exchange per round.  Two blocks of 256 threads per SM (64 KB of shared memory each).
+template <bool DIT>
+__global__ void __launch_bounds__(256, 2)
+k_ntt_r8(Fr *__restrict__ data, size_t vstride, const NttPass P, const Fr *__restrict__ tw, const Fr *__restrict__ post)
+{
+    extern __shared__ uint32_t sm[];
+    Fr *a = data + (size_t)blockIdx.y * vstride;
+    const int tid = threadIdx.x, T = blockDim.x;
+    ntt_tile_load(P, tid, T, sm, a, blockIdx.x);
+    __syncthreads();
+    for (int rd = 0; rd < P.nrounds; rd++) {
+        ntt_tile_round_any<DIT>(P, rd, tid, sm, blockIdx.x, tw);
+        __syncthreads();
+    }
+    ntt_tile_store(P, tid, T, sm, a, blockIdx.x, post);
+}
+
 // out[bitrev(i)] = in[i]
 __global__ void k_bitrev(const Fr *__restrict__ in, Fr *__restrict__ out, size_t vstride, int L)
 {
@@ -191,61 +211,66 @@ __global__ void k_h_finish(const Fr *__restrict__ a, size_t vstride, int L, cons
     if (h_plain) st_vec(h_plain + v * hstride + i, h.from_mont());
 }
 
-// natural-order variant for the step domain: h_i = a[i] * cos_inv[i]
-__global__ void k_h_finish_nat(const Fr *__restrict__ a, size_t vstride, size_t m, const Fr *__restrict__ cos_inv,
-                               Fr *__restrict__ h_mont, Fr *__restrict__ h_plain, size_t hstride)
-{
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
-    const size_t v = blockIdx.y;
-    const Fr h = ld_vec(a + v * vstride + i) * ld_vec_ro(cos_inv + i);
-    st_vec(h_mont + v * hstride + i, h);
-    if (h_plain) st_vec(h_plain + v * hstride + i, h.from_mont());
-}
-
 } // namespace
 
 namespace {
 
 // ---- step domain kernels (step_radix2_domain.tcc:39-146) ---------------------------------
-// FFT front end: out = [c (big) | e (small)]
-__global__ void k_step_fft_pre(const Fr *__restrict__ a, Fr *__restrict__ out, size_t vstride, size_t big, size_t small,
-                               const Fr *__restrict__ om_fwd)
+// The two power-of-two transforms of a step-domain FFT run decimation-in-time (bit-reversed in, natural out) and
+// those of an inverse run decimation-in-frequency (natural in, bit-reversed out); the permutation is folded into
+// the writes of the front end / the reads of the back end below, so no separate bit-reversal or copy pass exists.
+// FFT front end: out = [c (big, bit-reversed) | e (small, bit-reversed)]; in_tab (optional): a[i] *= in_tab[i] first
+__global__ void k_step_fft_pre(const Fr *__restrict__ a, Fr *__restrict__ out, size_t vstride, int lb, int ls,
+                               const Fr *__restrict__ om_fwd, const Fr *__restrict__ in_tab)
 {
+    const size_t big = (size_t)1 << lb, small = (size_t)1 << ls;
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= small) return;
     const Fr *x = a + (size_t)blockIdx.y * vstride;
     Fr *o = out + (size_t)blockIdx.y * vstride;
-    const Fr lo = ld_vec(x + i), hi = ld_vec(x + big + i);
-    st_vec(o + i, lo + hi);
+    Fr lo = ld_vec(x + i), hi = ld_vec(x + big + i);
+    if (in_tab) {
+        lo = lo * ld_vec_ro(in_tab + i);
+        hi = hi * ld_vec_ro(in_tab + big + i);
+    }
+    st_vec(o + brev((uint32_t)i, lb), lo + hi);
     Fr e = (lo - hi) * ld_vec_ro(om_fwd + i);
     for (size_t k = i + small; k < big; k += small) {
-        const Fr v = ld_vec(x + k);
-        st_vec(o + k, v);
+        Fr v = ld_vec(x + k);
+        if (in_tab) v = v * ld_vec_ro(in_tab + k);
+        st_vec(o + brev((uint32_t)k, lb), v);
         e = e + v * ld_vec_ro(om_fwd + k);
     }
-    st_vec(o + big + i, e);
+    st_vec(o + big + brev((uint32_t)i, ls), e);
 }
 
-// iFFT back end: u = [NTT_big^-1 (unscaled) | NTT_small^-1 (unscaled)] -> out = coefficients
-__global__ void k_step_ifft_post(const Fr *__restrict__ u, Fr *__restrict__ out, size_t vstride, size_t big,
-                                 size_t small, const Fr *__restrict__ om_fwd, const Fr *__restrict__ om_inv, Fr big_inv,
-                                 Fr small_inv, Fr half)
+// iFFT back end: u = [NTT_big^-1 (unscaled, bit-reversed) | NTT_small^-1 (unscaled, bit-reversed)] -> coefficients in
+// natural order, times out_tab[i] when given, to out (stride ostride) and, when plain != NULL, their plain form
+__global__ void k_step_ifft_post(const Fr *__restrict__ u, size_t vstride, Fr *__restrict__ out, Fr *__restrict__ plain,
+                                 size_t ostride, int lb, int ls, const Fr *__restrict__ om_fwd, const Fr *__restrict__ om_inv,
+                                 Fr big_inv, Fr small_inv, Fr half, const Fr *__restrict__ out_tab)
 {
+    const size_t big = (size_t)1 << lb, small = (size_t)1 << ls;
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= small) return;
     const Fr *x = u + (size_t)blockIdx.y * vstride;
-    Fr *o = out + (size_t)blockIdx.y * vstride;
-    const Fr u0 = ld_vec(x + i) * big_inv;
-    Fr u1 = ld_vec(x + big + i) * small_inv;
+    Fr *o = out + (size_t)blockIdx.y * ostride;
+    Fr *pl = plain ? plain + (size_t)blockIdx.y * ostride : nullptr;
+    auto emit = [&](size_t idx, Fr v) {
+        if (out_tab) v = v * ld_vec_ro(out_tab + idx);
+        st_vec(o + idx, v);
+        if (pl) st_vec(pl + idx, v.from_mont());
+    };
+    const Fr u0 = ld_vec(x + brev((uint32_t)i, lb)) * big_inv;
+    Fr u1 = ld_vec(x + big + brev((uint32_t)i, ls)) * small_inv;
     for (size_t k = i + small; k < big; k += small) {
-        const Fr v = ld_vec(x + k) * big_inv;
-        st_vec(o + k, v);
+        const Fr v = ld_vec(x + brev((uint32_t)k, lb)) * big_inv;
+        emit(k, v);
         u1 = u1 - v * ld_vec_ro(om_fwd + k);
     }
     u1 = u1 * ld_vec_ro(om_inv + i);
-    st_vec(o + i, (u0 + u1) * half);
-    st_vec(o + big + i, (u0 - u1) * half);
+    emit(i, (u0 + u1) * half);
+    emit(big + i, (u0 - u1) * half);
 }
 
 // 1 / Z(g x_i) on the coset (step_radix2_domain.tcc:222-246)
@@ -338,27 +363,37 @@ int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, si
     if (!(ctx->func_attr_done & 1u)) { // per device = per context
         ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_pass<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
         ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_pass<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         ctx->func_attr_done |= 1u;
     }
-    const int P = (L + NTT_KMAX - 1) / NTT_KMAX;
-    int ks[8];
-    for (int p = 0; p < P; p++) ks[p] = L / P + (p < L % P ? 1 : 0);
+    static const int tile_log = [] { // development knob: ZKB_NTT_TILE = 10 or 11
+        const char *e = getenv("ZKB_NTT_TILE");
+        const int v = e ? atoi(e) : 0;
+        return v == 10 || v == 11 ? v : NTT_TILE_DEFAULT;
+    }();
+    NttPlan pl;
+    ntt_plan_transform(&pl, L, dit, tile_log);
     const Fr *tw = inverse ? T.inv : T.fwd;
-    int done = 0;
-    for (int p = 0; p < P; p++) {
-        const int k = ks[p];
-        const int lobits = dit ? done : (L - done - k);
-        int logC = 0;
-        while ((2 << logC << k) <= NTT_EMAX && logC + 1 <= L - k) logC++;
-        const unsigned blocks = 1u << (L - k - logC);
-        const size_t smem = ((size_t)32 << k) << logC;
-        const bool last = p == P - 1;
-        if (dit)
-            k_ntt_pass<true><<<dim3(blocks, nvec), NTT_T, smem, ctx->stream>>>(a, vstride, L, lobits, k, logC, tw, last ? post : nullptr);
-        else
-            k_ntt_pass<false><<<dim3(blocks, nvec), NTT_T, smem, ctx->stream>>>(a, vstride, L, lobits, k, logC, tw, last ? post : nullptr);
+    for (int p = 0; p < pl.npass; p++) {
+        const NttPass &P = pl.pass[p];
+        const unsigned blocks = 1u << (L - P.k - P.logC);
+        const size_t smem = ((size_t)32 << P.k) << P.logC;
+        const Fr *pp = p == pl.npass - 1 ? post : nullptr;
+        if (pl.r8[p]) {
+            const unsigned threads = 1u << (P.k + P.logC - 3);
+            if (dit)
+                k_ntt_r8<true><<<dim3(blocks, nvec), threads, smem, ctx->stream>>>(a, vstride, P, tw, pp);
+            else
+                k_ntt_r8<false><<<dim3(blocks, nvec), threads, smem, ctx->stream>>>(a, vstride, P, tw, pp);
+        } else if (dit) { // transforms below 256 points
+            k_ntt_pass<true><<<dim3(blocks, nvec), NTT_T, smem, ctx->stream>>>(a, vstride, L, P.lobits, P.k, P.logC, tw, pp);
+        } else {
+            k_ntt_pass<false><<<dim3(blocks, nvec), NTT_T, smem, ctx->stream>>>(a, vstride, L, P.lobits, P.k, P.logC, tw, pp);
+        }
         ZKB_LAUNCH_CHECK(ctx);
-        done += k;
     }
     return ZKB_OK;
 }
@@ -484,30 +519,37 @@ int domain_build(zkb_ctx *ctx, size_t m, int kind, Domain *d)
     return ZKB_OK;
 }
 
-// ---- step domain, natural order (step_radix2_domain.tcc:39-146) ------------------------------
-static int step_fft(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp)
+// ---- step domain (step_radix2_domain.tcc:39-146) ------------------------------------------------------------
+// FFT of src (natural order, optionally pre-multiplied by in_tab) -> dst (natural order); src is left intact
+static int step_fft(zkb_ctx *ctx, const Domain *d, const Fr *src, Fr *dst, size_t vstride, int nvec, const Fr *in_tab)
 {
-    k_step_fft_pre<<<dim3(ceil_div(d->small_m, 128), nvec), 128, 0, ctx->stream>>>(a, tmp, vstride, d->big_m, d->small_m, d->om_fwd);
+    const int lb = d->big.logn, ls = d->small.logn;
+    k_step_fft_pre<<<dim3(ceil_div(d->small_m, 128), nvec), 128, 0, ctx->stream>>>(src, dst, vstride, lb, ls, d->om_fwd, in_tab);
     ZKB_LAUNCH_CHECK(ctx);
-    int rc = r2_natural(ctx, d->big, false, tmp, vstride, nvec, a);
-    if (!rc) rc = r2_natural(ctx, d->small, false, tmp + d->big_m, vstride, nvec, a + d->big_m);
-    if (rc) return rc;
-    ZKB_CUDA(ctx, cudaMemcpy2DAsync(a, vstride * sizeof(Fr), tmp, vstride * sizeof(Fr), d->m * sizeof(Fr), nvec,
-                                    cudaMemcpyDeviceToDevice, ctx->stream));
-    return ZKB_OK;
+    int rc = r2_levels(ctx, d->big, false, true, dst, vstride, nvec, nullptr);
+    if (!rc) rc = r2_levels(ctx, d->small, false, true, dst + d->big_m, vstride, nvec, nullptr);
+    return rc;
 }
 
-static int step_ifft(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp)
+// iFFT of a (natural order; destroyed) -> out (natural order, stride ostride), times out_tab[i] when given;
+// plain != NULL also receives the plain-integer form
+static int step_ifft(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *out, Fr *plain, size_t ostride,
+                     const Fr *out_tab)
 {
-    int rc = r2_natural(ctx, d->big, true, a, vstride, nvec, tmp);
-    if (!rc) rc = r2_natural(ctx, d->small, true, a + d->big_m, vstride, nvec, tmp + d->big_m);
+    int rc = r2_levels(ctx, d->big, true, false, a, vstride, nvec, nullptr);
+    if (!rc) rc = r2_levels(ctx, d->small, true, false, a + d->big_m, vstride, nvec, nullptr);
     if (rc) return rc;
     const Fr big_inv = fr_from_u64(d->big_m).inverse(), small_inv = fr_from_u64(d->small_m).inverse();
     const Fr half = fr_from_u64(2).inverse();
-    k_step_ifft_post<<<dim3(ceil_div(d->small_m, 128), nvec), 128, 0, ctx->stream>>>(a, tmp, vstride, d->big_m, d->small_m, d->om_fwd,
-                                                                                   d->om_inv, big_inv, small_inv, half);
+    k_step_ifft_post<<<dim3(ceil_div(d->small_m, 128), nvec), 128, 0, ctx->stream>>>(
+        a, vstride, out, plain, ostride, d->big.logn, d->small.logn, d->om_fwd, d->om_inv, big_inv, small_inv, half, out_tab);
     ZKB_LAUNCH_CHECK(ctx);
-    ZKB_CUDA(ctx, cudaMemcpy2DAsync(a, vstride * sizeof(Fr), tmp, vstride * sizeof(Fr), d->m * sizeof(Fr), nvec,
+    return ZKB_OK;
+}
+
+static int copy_back(zkb_ctx *ctx, Fr *a, const Fr *tmp, size_t vstride, size_t m, int nvec)
+{
+    ZKB_CUDA(ctx, cudaMemcpy2DAsync(a, vstride * sizeof(Fr), tmp, vstride * sizeof(Fr), m * sizeof(Fr), nvec,
                                     cudaMemcpyDeviceToDevice, ctx->stream));
     return ZKB_OK;
 }
@@ -520,10 +562,13 @@ int domain_op(zkb_ctx *ctx, const Domain *d, int op, Fr *a, size_t vstride, int 
     int rc = ZKB_OK;
     switch (op) {
     case ZKB_NTT_COSET_FFT:
-        if ((rc = scale(ctx, a, vstride, d->m, nvec, d->cos_fwd, basic ? &m_scal : nullptr))) return rc;
-        /* fall through */
     case ZKB_NTT_FFT:
-        return basic ? r2_natural(ctx, d->big, false, a, vstride, nvec, tmp) : step_fft(ctx, d, a, vstride, nvec, tmp);
+        if (basic) {
+            if (op == ZKB_NTT_COSET_FFT && (rc = scale(ctx, a, vstride, d->m, nvec, d->cos_fwd, &m_scal))) return rc;
+            return r2_natural(ctx, d->big, false, a, vstride, nvec, tmp);
+        }
+        if ((rc = step_fft(ctx, d, a, tmp, vstride, nvec, op == ZKB_NTT_COSET_FFT ? d->cos_fwd : nullptr))) return rc;
+        return copy_back(ctx, a, tmp, vstride, d->m, nvec);
     case ZKB_NTT_IFFT:
     case ZKB_NTT_ICOSET_FFT:
         if (basic) {
@@ -532,8 +577,8 @@ int domain_op(zkb_ctx *ctx, const Domain *d, int op, Fr *a, size_t vstride, int 
             return op == ZKB_NTT_IFFT ? scale(ctx, a, vstride, d->m, nvec, nullptr, &minv)
                                       : scale(ctx, a, vstride, d->m, nvec, d->cos_inv, nullptr);
         }
-        if ((rc = step_ifft(ctx, d, a, vstride, nvec, tmp))) return rc;
-        return op == ZKB_NTT_IFFT ? ZKB_OK : scale(ctx, a, vstride, d->m, nvec, d->cos_inv, nullptr);
+        if ((rc = step_ifft(ctx, d, a, vstride, nvec, tmp, nullptr, vstride, op == ZKB_NTT_IFFT ? nullptr : d->cos_inv))) return rc;
+        return copy_back(ctx, a, tmp, vstride, d->m, nvec);
     case ZKB_NTT_DIV_Z_ON_COSET:
         return basic ? scale(ctx, a, vstride, d->m, nvec, nullptr, &d->zinv) : scale(ctx, a, vstride, d->m, nvec, d->zinv_tab, nullptr);
     default:
@@ -549,30 +594,27 @@ int domain_to_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nv
         if (!rc) rc = r2_levels(ctx, d->big, false, true, a, vstride, nvec, nullptr);
         return rc;
     }
-    int rc = step_ifft(ctx, d, a, vstride, nvec, tmp);
-    if (!rc) rc = scale(ctx, a, vstride, d->m, nvec, d->cos_fwd, nullptr);
-    if (!rc) rc = step_fft(ctx, d, a, vstride, nvec, tmp);
+    // coefficients times g^i land in tmp, the forward transform brings them back to a: no copy, no permutation pass
+    int rc = step_ifft(ctx, d, a, vstride, nvec, tmp, nullptr, vstride, d->cos_fwd);
+    if (!rc) rc = step_fft(ctx, d, tmp, a, vstride, nvec, nullptr);
     return rc;
 }
 
 int domain_h_from_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp, Fr *h_mont, Fr *h_plain,
                         size_t hstride)
 {
-    const dim3 grid(ceil_div(d->m, 128), nvec);
+    // 1 / Z on the coset is the caller's: a constant for the basic domain (it commutes with the transform), the
+    // table Domain::zinv_tab for the step domain -- both belong in the caller's pointwise pass
+    (void)tmp;
     if (d->kind == ZKB_DOMAIN_BASIC_RADIX2) {
-        // the constant 1 / Z(g) commutes with the transform: folded into the caller's pointwise pass
+        const dim3 grid(ceil_div(d->m, 128), nvec);
         int rc = r2_levels(ctx, d->big, true, false, a, vstride, nvec, nullptr);
         if (rc) return rc;
         k_h_finish<<<grid, 128, 0, ctx->stream>>>(a, vstride, d->big.logn, d->cos_inv, h_mont, h_plain, hstride);
         ZKB_LAUNCH_CHECK(ctx);
         return ZKB_OK;
     }
-    int rc = scale(ctx, a, vstride, d->m, nvec, d->zinv_tab, nullptr);
-    if (!rc) rc = step_ifft(ctx, d, a, vstride, nvec, tmp);
-    if (rc) return rc;
-    k_h_finish_nat<<<grid, 128, 0, ctx->stream>>>(a, vstride, d->m, d->cos_inv, h_mont, h_plain, hstride);
-    ZKB_LAUNCH_CHECK(ctx);
-    return ZKB_OK;
+    return step_ifft(ctx, d, a, vstride, nvec, h_mont, h_plain, hstride, d->cos_inv);
 }
 
 } // namespace zkb

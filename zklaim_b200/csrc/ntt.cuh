@@ -43,7 +43,8 @@ void domain_free(Domain *d);
 // tmp: scratch of the same shape (used by the natural-order paths).
 // a <- cosetFFT(iFFT(a), g): evaluations on the domain -> evaluations on the coset (r1cs_to_qap.tcc:239-268)
 int domain_to_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp);
-// h <- icosetFFT(divide_by_Z_on_coset(a), g) (r1cs_to_qap.tcc:301-311); a is destroyed.
+// h <- icosetFFT(a, g) (r1cs_to_qap.tcc:306-311); a is destroyed.  divide_by_Z_on_coset (:301-303) is the caller's:
+// it multiplies by Domain::zinv (basic) or Domain::zinv_tab[i] (step) in its pointwise pass.
 // Writes m coefficients in natural order to h_mont + v * hstride (Montgomery) and, when
 // h_plain != NULL, their plain-integer form to h_plain + v * hstride.
 int domain_h_from_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp, Fr *h_mont,

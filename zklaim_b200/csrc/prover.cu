@@ -52,6 +52,7 @@ struct zkb_key {
     MsmPlan g1ab, g1c, g2;              // see the header: jobs {A, B1}, {C}, {B2}
     std::vector<uint32_t> h_sidx[3];    // host copies of the scalar maps (g1ab, g1c, g2), for zkb_key_tune
     size_t nnzB = 0;
+    bool cs_only = false;                // uploaded without queries: zkb_witness_map only
     int shard_rank = 0, shard_world = 1; // which contiguous range of every query this key holds
     size_t zlen = 0; // elements per row of Z
     size_t bytes = 0;
@@ -192,8 +193,9 @@ __global__ void k_sat_check(const Fr *__restrict__ abc, size_t nc, size_t m, int
     if (a * b != c) atomicOr(flags + p, 1u);
 }
 
-// A <- (A * B - C) [* zinv]   on the coset (r1cs_to_qap.tcc:270-303)
-__global__ void k_h_pointwise(Fr *__restrict__ abc, size_t m, int batch, Fr zinv, int use_zinv)
+// A <- (A * B - C) / Z   on the coset (r1cs_to_qap.tcc:270-303); 1 / Z is the constant zinv (basic domain) or
+// zinv_tab[i] (step domain, step_radix2_domain.tcc:222-246)
+__global__ void k_h_pointwise(Fr *__restrict__ abc, size_t m, int batch, Fr zinv, const Fr *__restrict__ zinv_tab)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= m) return;
@@ -201,8 +203,7 @@ __global__ void k_h_pointwise(Fr *__restrict__ abc, size_t m, int batch, Fr zinv
     Fr *a = abc + ((size_t)0 * batch + p) * m + i;
     const Fr b = ld_vec(abc + ((size_t)1 * batch + p) * m + i);
     const Fr c = ld_vec(abc + ((size_t)2 * batch + p) * m + i);
-    Fr h = ld_vec(a) * b - c;
-    if (use_zinv) h = h * zinv;
+    const Fr h = (ld_vec(a) * b - c) * (zinv_tab ? ld_vec_ro(zinv_tab + i) : zinv);
     st_vec(a, h);
 }
 
@@ -502,9 +503,10 @@ int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key, int rank, int w
     if (domain_select_host(key->nc + ni + 1, &key->m, &key->kind))
         return fail(ctx, ZKB_ERR_DOMAIN, "zkb_key_upload: no supported evaluation domain for this constraint system");
     const size_t m = key->m;
-    if (d->H_size != m - 1) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: H_query size must be domain size - 1");
+    key->cs_only = d->A_query == nullptr;
+    if (!key->cs_only && d->H_size != m - 1) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: H_query size must be domain size - 1");
     if (nv + m + 8 >= (1ull << 31)) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: key too large");
-    for (size_t k = 0; k < d->B_nnz; k++)
+    for (size_t k = 0; d->B_index && k < d->B_nnz; k++)
         if (d->B_index[k] > nv) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: B_query index out of range");
     int rc;
     if ((rc = domain_build(ctx, m, key->kind, &key->dom))) return rc;
@@ -523,6 +525,10 @@ int key_build(zkb_ctx *ctx, const zkb_key_desc *d, zkb_key *key, int rank, int w
     }
     key->zlen = (nv + 4 + m + 1 + 3) & ~(size_t)3;
     key->nnzB = d->B_nnz;
+    if (key->cs_only) { // the constraint system and its domain are all zkb_witness_map needs
+        ZKB_CUDA(ctx, cudaDeviceSynchronize());
+        return ZKB_OK;
+    }
 
     // ---- MSM plans: {A, B1}, {C} in G1 and {B2} in G2 ----
     // A shard (rank of world) keeps the contiguous range [lo, hi) of every query -- libff's own chunking,
@@ -723,7 +729,7 @@ int witness_map_chunk(zkb_ctx *ctx, const zkb_key *key, int batch, uint32_t *d_f
     int rc = domain_to_coset(ctx, &key->dom, abc, m, 3 * batch, tmp);
     if (rc) return rc;
     const bool basic = key->kind == ZKB_DOMAIN_BASIC_RADIX2;
-    k_h_pointwise<<<dim3(ceil_div(m, 128), batch), 128, 0, st>>>(abc, m, batch, key->dom.zinv, basic ? 1 : 0);
+    k_h_pointwise<<<dim3(ceil_div(m, 128), batch), 128, 0, st>>>(abc, m, batch, key->dom.zinv, basic ? nullptr : key->dom.zinv_tab);
     ZKB_LAUNCH_CHECK(ctx);
     return domain_h_from_coset(ctx, &key->dom, abc, m, batch, tmp, Z + key->z_h(), P + key->z_h(), key->zlen);
 }
@@ -802,6 +808,7 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
 {
     if (!ctx || !key || !w || (!map_only && (!r || !s || (!out && !part_out)))) return fail(ctx, ZKB_ERR_ARG, "zkb_prove: bad argument");
     if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_prove: key lives on another device");
+    if (!map_only && key->cs_only) return fail(ctx, ZKB_ERR_ARG, "zkb_prove: this key was uploaded without queries (witness map only)");
     if (!map_only && !part_out && key->shard_world != 1)
         return fail(ctx, ZKB_ERR_ARG, "zkb_prove: this key holds one shard of the queries: use zkb_prove_partial + zkb_prove_combine");
     const bool partial = part_out != nullptr;
@@ -814,6 +821,7 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
     const cudaMemcpyKind kin = dev_in ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     double total_ms = 0;
     bool unsat = false;
+    ctx->batch_status.assign(count, 0);
     for (size_t base = 0; base < count; base += chunk) {
         const int batch = (int)((count - base < (size_t)chunk) ? count - base : chunk);
         ZKB_CUDA(ctx, ctx->scratch[SP_Z].ensure((size_t)batch * zlen * sizeof(Fr)));
@@ -859,7 +867,14 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
         prof_collect(ctx);
         if (!map_only && partial) memcpy(part_out + base, ctx->pinned, (size_t)batch * sizeof(zkb_partial));
         if (!map_only && !partial) memcpy(out + base, ctx->pinned, (size_t)batch * sizeof(zkb_proof));
-        for (int p = 0; p < batch; p++) unsat |= h_flags[p] != 0;
+        for (int p = 0; p < batch; p++) {
+            if (!h_flags[p]) continue;
+            unsat = true;
+            ctx->batch_status[base + p] = ZKB_ERR_UNSAT;
+            // what the arithmetic produced for an unsatisfying assignment is not a proof: hand back zeros
+            if (!map_only && partial) memset(part_out + base + p, 0, sizeof(zkb_partial));
+            if (!map_only && !partial) memset(out + base + p, 0, sizeof(zkb_proof));
+        }
     }
     ctx->last_ms = total_ms;
     if (unsat) return fail(ctx, ZKB_ERR_UNSAT, "the witness does not satisfy the constraint system");
@@ -876,9 +891,12 @@ int zkb_key_upload_shard(zkb_ctx *ctx, const zkb_key_desc *desc, int rank, int w
 {
     if (!ctx || !desc || !out) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: bad argument");
     if (world < 1 || rank < 0 || rank >= world) return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload_shard: bad rank / world");
-    if (!desc->alpha_g1 || !desc->beta_g1 || !desc->delta_g1 || !desc->beta_g2 || !desc->delta_g2 || !desc->A_query ||
-        !desc->H_query || (desc->B_nnz && (!desc->B_index || !desc->B_g1 || !desc->B_g2)) ||
-        (desc->num_variables > desc->num_inputs && !desc->L_query))
+    const bool no_queries = !desc->alpha_g1 && !desc->beta_g1 && !desc->delta_g1 && !desc->beta_g2 && !desc->delta_g2 &&
+                            !desc->A_query && !desc->H_query && !desc->L_query && !desc->B_g1 && !desc->B_g2;
+    if (!no_queries &&
+        (!desc->alpha_g1 || !desc->beta_g1 || !desc->delta_g1 || !desc->beta_g2 || !desc->delta_g2 || !desc->A_query ||
+         !desc->H_query || (desc->B_nnz && (!desc->B_index || !desc->B_g1 || !desc->B_g2)) ||
+         (desc->num_variables > desc->num_inputs && !desc->L_query)))
         return fail(ctx, ZKB_ERR_ARG, "zkb_key_upload: missing key arrays");
     ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
     zkb_key *key = new zkb_key();
@@ -895,6 +913,7 @@ int zkb_key_tune(zkb_ctx *ctx, zkb_key *key, const uint64_t *w)
 {
     if (!ctx || !key || !w) return fail(ctx, ZKB_ERR_ARG, "zkb_key_tune: bad argument");
     if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_key_tune: key lives on another device");
+    if (key->cs_only) return ZKB_OK;
     ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
     ZKB_CUDA(ctx, cudaDeviceSynchronize());
     static const uint64_t one_r[4] = {0xac96341c4ffffffbull, 0x36fc76959f60cd29ull, 0x666ea36f7879462eull, 0x0e0a77c19a07df2full};
@@ -932,6 +951,10 @@ int zkb_key_tune(zkb_ctx *ctx, zkb_key *key, const uint64_t *w)
 int zkb_key_windows(const zkb_key *key, int out[4])
 {
     if (!key || !out) return ZKB_ERR_ARG;
+    if (key->cs_only) {
+        out[0] = out[1] = out[2] = out[3] = 0;
+        return ZKB_OK;
+    }
     out[0] = key->g1ab.tab.j[0].c;
     out[1] = key->g1ab.tab.j[1].c;
     out[2] = key->g1c.tab.j[0].c;
@@ -942,6 +965,13 @@ int zkb_key_windows(const zkb_key *key, int out[4])
 void zkb_key_free(zkb_key *key) { key_release(key); }
 
 size_t zkb_key_device_bytes(const zkb_key *key) { return key ? key->bytes : 0; }
+
+int zkb_key_num_variables(const zkb_key *key, size_t *nv_out)
+{
+    if (!key || !nv_out) return ZKB_ERR_ARG;
+    *nv_out = key->nv;
+    return ZKB_OK;
+}
 
 int zkb_key_domain(const zkb_key *key, size_t *m_out, int *kind_out)
 {
@@ -1007,6 +1037,13 @@ int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64
                     zkb_proof *out)
 {
     return prove_impl(ctx, key, count, w, r, s, false, out, nullptr, false);
+}
+
+int zkb_prove_batch_status(const zkb_ctx *ctx, int32_t *status, size_t n)
+{
+    if (!ctx || (!status && n)) return ZKB_ERR_ARG;
+    for (size_t i = 0; i < n; i++) status[i] = i < ctx->batch_status.size() ? ctx->batch_status[i] : 0;
+    return ZKB_OK;
 }
 
 int zkb_prove_batch_submit(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r, const uint64_t *s)
