@@ -26,6 +26,8 @@
 #include <fcntl.h>
 #include <openssl/sha.h>
 
+#include <libsnark/gadgetlib1/gadgets/hashes/sha256/sha256_gadget.hpp>
+
 #include "zkb_libsnark.hpp"
 
 using namespace zkb_bridge;
@@ -739,6 +741,112 @@ int zkbr_setup_roundtrip(size_t payloads, uint64_t seed, int stock, double *seco
     const int rc = libsnark_verify(&c.ctx);
     seconds[2] = now_s() - t;
     return rc;
+}
+
+/* ---- BASELINE.json config #5 for bench.py: "synthetic 2^22-constraint R1CS (chained SHA-256 gadgets)" ---------------
+ * `blocks` chained libsnark sha256_two_to_one_hash_gadgets (gadgetlib1/gadgets/hashes/sha256/sha256_gadget.hpp; the
+ * same gadget zklaim's commitment uses, zklaim_gadget.cpp) with a satisfying assignment from `seed`; the final digest's
+ * 256 bits are the public input.  153 blocks = 4 173 840 constraints = domain 2^22.  The constraint system is handed
+ * out as the CSR arrays of zkb_setup_desc / zkb_key_desc; the key comes from zkb_setup. */
+namespace {
+struct Synth {
+    r1cs_constraint_system<FrT> cs;
+    std::vector<FrT> primary, auxiliary;
+};
+} // namespace
+
+void *zkbr_synth_sha_chain(size_t blocks, uint64_t seed)
+{
+    StdoutMute mute;
+    ppT::init_public_params();
+    try {
+        Synth *sy = new Synth();
+        protoboard<FrT> pb;
+        std::vector<std::shared_ptr<digest_variable<FrT>>> dig(blocks + 1), right(blocks);
+        dig[blocks].reset(new digest_variable<FrT>(pb, 256, "out")); /* allocated first: the primary input */
+        pb.set_input_sizes(256);
+        for (size_t i = 0; i < blocks; i++) dig[i].reset(new digest_variable<FrT>(pb, 256, "d"));
+        for (size_t i = 0; i < blocks; i++) right[i].reset(new digest_variable<FrT>(pb, 256, "r"));
+        std::vector<std::shared_ptr<sha256_two_to_one_hash_gadget<FrT>>> h(blocks);
+        for (size_t i = 0; i < blocks; i++) {
+            h[i].reset(new sha256_two_to_one_hash_gadget<FrT>(pb, *dig[i], *right[i], *dig[i + 1], "h"));
+            h[i]->generate_r1cs_constraints();
+        }
+        uint64_t x = seed * 0x9e3779b97f4a7c15ull + 0x1234567;
+        auto bits = [&]() {
+            libff::bit_vector v(256);
+            for (size_t j = 0; j < 256; j++) {
+                x ^= x << 13;
+                x ^= x >> 7;
+                x ^= x << 17;
+                v[j] = x & 1;
+            }
+            return v;
+        };
+        dig[0]->generate_r1cs_witness(bits());
+        for (size_t i = 0; i < blocks; i++) {
+            right[i]->generate_r1cs_witness(bits());
+            h[i]->generate_r1cs_witness();
+        }
+        sy->cs = pb.get_constraint_system();
+        sy->primary = pb.primary_input();
+        sy->auxiliary = pb.auxiliary_input();
+        return sy;
+    } catch (const std::exception &e) {
+        fprintf(stderr, "zkbr_synth_sha_chain: %s\n", e.what());
+        return NULL;
+    }
+}
+
+void zkbr_synth_free(void *h) { delete (Synth *)h; }
+
+/* dims[0..6) = num_constraints, num_variables, num_inputs, nnz(A), nnz(B), nnz(C) */
+void zkbr_synth_dims(void *h, size_t *dims)
+{
+    Synth *sy = (Synth *)h;
+    dims[0] = sy->cs.num_constraints();
+    dims[1] = sy->cs.num_variables();
+    dims[2] = sy->cs.num_inputs();
+    size_t nnz[3] = {0, 0, 0};
+    for (const auto &c : sy->cs.constraints) {
+        nnz[0] += c.a.terms.size();
+        nnz[1] += c.b.terms.size();
+        nnz[2] += c.c.terms.size();
+    }
+    dims[3] = nnz[0];
+    dims[4] = nnz[1];
+    dims[5] = nnz[2];
+}
+
+/* matrix `which` (0 = A, 1 = B, 2 = C) as CSR: row_ptr (num_constraints + 1), col (nnz), coeff (nnz x 4 limbs) */
+void zkbr_synth_csr(void *h, int which, uint64_t *row_ptr, uint32_t *col, uint64_t *coeff)
+{
+    Synth *sy = (Synth *)h;
+    size_t k = 0, row = 0;
+    row_ptr[0] = 0;
+    for (const auto &c : sy->cs.constraints) {
+        const linear_combination<FrT> &lc = which == 0 ? c.a : (which == 1 ? c.b : c.c);
+        for (const auto &t : lc.terms) {
+            col[k] = (uint32_t)t.index;
+            put_fr(coeff + 4 * k, t.coeff);
+            k++;
+        }
+        row_ptr[++row] = k;
+    }
+}
+
+void zkbr_synth_witness(void *h, uint64_t *w)
+{
+    Synth *sy = (Synth *)h;
+    pack_assignment(sy->primary, sy->auxiliary, w);
+}
+
+/* the curve's generators as Jacobian limbs (12 + 24): what zkb_setup takes as g1_generator / g2_generator */
+void zkbr_generators(uint64_t *g1_jac, uint64_t *g2_jac)
+{
+    ppT::init_public_params();
+    put_g1_jacobian(g1_jac, G1T::one());
+    put_g2_jacobian(g2_jac, G2T::one());
 }
 
 } // extern "C"

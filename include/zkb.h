@@ -335,6 +335,10 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
                      int32_t *accept);
 
 /* ---- measurement helpers (used by bench.py only) ------------------------------------ */
+/* n distinct G1 bases k_i * G generated ON the device (k_i = 252 bits of a counter-based hash of (seed, i)) and held as
+ * zkb_bases_upload would hold them: the MSM sweep of BASELINE config #3 needs 2^24 random points, which are 1 GB to
+ * make on the host and push.  Parity of the MSM itself is tested on host-made bases (tests/test_gpu_large.py). */
+int zkb_bases_synthetic(zkb_ctx *ctx, size_t n, uint64_t seed, int window_bits, int precompute_factor, zkb_bases **out);
 /* Sustained integer multiply-add rate of the device, measured with chains of dependent Fq Montgomery
  * products (136 multiply-adds of 32 x 32 + 64 -> 64 bits each, the instruction mix of every kernel here) on
  * all SMs; `iters` = products per chain / 2 (0 = default).  Returns multiply-adds per second, < 0 on error. */

@@ -100,3 +100,90 @@ def test_key_table_cache_follows_the_verification_key(zctx, ref):
         # proofs of key 2 under key 1: rejected
         assert zctx.verify_batch(vk1, x2, pr2).tolist() == [False, False, False]
     circ.free()
+
+
+@pytest.mark.parametrize("n", [200, 1100])
+def test_all_kernel_forms_decide_like_the_reference(zctx, ref, n):
+    """zkb_verify_batch / zkb_pairing pick one of three kernel forms by batch size (18 lanes per pairing up to 128
+    proofs, 6 lanes up to 1 024, one lane above): the golden batch tiled to n = 200 (6-lane form) and n = 1 100 (one-lane
+    form) with tampered A / B / C (a point off its curve, the point at infinity, elements swapped between proofs) and a
+    wrong public input.  Every decision must equal r1cs_gg_ppzksnark_verifier_strong_IC's (r1cs_gg_ppzksnark.tcc:523-622)
+    on the same proof; pairing values at the same batch sizes must equal the golden Miller / reduced values."""
+    g = np.load(os.path.join(GOLD, "verify.npz"))
+    vk = {k: g[k] for k in ("alpha_g1_beta_g2", "gamma_g2", "delta_g2", "gamma_ABC_g1")}
+    ni = len(vk["gamma_ABC_g1"]) - 1
+    reps = (n + 7) // 8
+    primary = np.tile(g["primary"], (reps, 1, 1))[:n].copy()
+    proofs = np.tile(g["proofs"], (reps, 1))[:n].copy()
+    exp = np.tile(g["accept"].astype(bool), reps)[:n].copy()
+    # tamper with proofs that are valid in the golden batch (indices = 0 .. 3 mod 8), spread over the batch
+    valid = [i for i in range(n) if exp[i]]
+    pick = [valid[k * len(valid) // 9] for k in range(9)]
+    one_q = ref.field_const(zk.FQ, 1)
+    proofs[pick[0], 0] ^= np.uint64(4)                           # A off the curve
+    proofs[pick[1], 0:12] = 0                                    # A = infinity (0, 1, 0)
+    proofs[pick[1], 4:8] = one_q
+    proofs[pick[2], 12] ^= np.uint64(2)                          # B off the twist
+    proofs[pick[3], 12:36] = 0                                   # B = infinity
+    proofs[pick[3], 20:24] = one_q
+    proofs[pick[4], 36] ^= np.uint64(8)                          # C off the curve
+    proofs[pick[5], 36:48] = 0                                   # C = infinity
+    proofs[pick[5], 40:44] = one_q
+    a6, c6 = proofs[pick[6], 0:12].copy(), proofs[pick[6], 36:48].copy()
+    proofs[pick[6], 0:12], proofs[pick[6], 36:48] = c6, a6       # A and C swapped inside a proof
+    proofs[pick[7], 36:48] = proofs[pick[8], 36:48]              # C of another (valid) proof with other randomness
+    primary[pick[8], ni - 1] = ref.sha512_rng(99, 1)[0]          # a wrong public input
+    acc = zctx.verify_batch(vk, primary, proofs)
+    # untouched proofs keep the golden decision; every tampering above invalidates a proof that was valid
+    want = exp.copy()
+    want[pick] = False
+    same_c = np.array_equal(g["proofs"][pick[7] % 8, 36:48], g["proofs"][pick[8] % 8, 36:48])
+    if same_c:
+        want[pick[7]] = True  # tiling made both proofs identical: replacing C by itself changes nothing
+    assert acc.tolist() == want.tolist()
+    # pairing values at this batch size (the same three kernel forms)
+    gp = np.load(os.path.join(GOLD, "pairing.npz"))
+    reps = (n + 5) // 6
+    P, Q = np.tile(gp["P"], (reps, 1))[:n], np.tile(gp["Q"], (reps, 1))[:n]
+    for reduced in (False, True):
+        got = zctx.pairing(P, Q, reduced)
+        assert np.array_equal(got, np.tile(gp["reduced" if reduced else "miller"], (reps, 1))[:n])
+
+
+@pytest.mark.parametrize("n", [200, 1100])
+def test_kernel_forms_against_the_live_reference_verifier(zctx, ref, n):
+    """the same three forms on proofs of a circuit the reference holds in full (its verifier runs on each tampered proof)"""
+    ni = 5
+    circ = ref.Circuit.example(41, ni, seed=41)
+    circ.setup()
+    w = circ.witness()
+    base = np.stack([circ.prove(w, ref.sha512_rng(170 + k, 1)[0], ref.sha512_rng(180 + k, 1)[0], want_H=False)["proof"]
+                     for k in range(4)]).reshape(4, 48)
+    vk = circ.export_vk()
+    vk["alpha_g1_beta_g2"] = circ.vk_alpha_beta()
+    proofs = np.tile(base, ((n + 3) // 4, 1))[:n].copy()
+    primary = np.tile(w[:ni], (n, 1, 1)).copy()
+    one_q = ref.field_const(zk.FQ, 1)
+    t = [3, n // 7, n // 5, n // 3, n // 2, n - 70, n - 33, n - 2, n - 1]
+    proofs[t[0], 1] ^= np.uint64(1)
+    proofs[t[1], 0:12] = 0
+    proofs[t[1], 4:8] = one_q
+    proofs[t[2], 13] ^= np.uint64(1)
+    proofs[t[3], 12:36] = 0
+    proofs[t[3], 20:24] = one_q
+    proofs[t[4], 37] ^= np.uint64(1)
+    proofs[t[5], 36:48] = 0
+    proofs[t[5], 40:44] = one_q
+    proofs[t[6], 36:48] = proofs[(t[6] + 1), 36:48]   # C of the neighbouring proof (other r, s)
+    primary[t[7], 0] = ref.sha512_rng(5, 1)[0]
+    a, c = proofs[t[8], 0:12].copy(), proofs[t[8], 36:48].copy()
+    proofs[t[8], 0:12], proofs[t[8], 36:48] = c, a
+    acc = zctx.verify_batch(vk, primary, proofs)
+    want = np.ones(n, dtype=bool)
+    for i in t:
+        want[i] = circ.verify(primary[i], proofs[i])
+    assert not want[t].any()
+    for i in (0, 1, n // 4, n - 3):
+        assert circ.verify(primary[i], proofs[i])
+    assert acc.tolist() == want.tolist()
+    circ.free()

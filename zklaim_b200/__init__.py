@@ -31,7 +31,7 @@ OP_ADD, OP_SUB, OP_MUL, OP_SQR, OP_INV, OP_NEG = range(6)
 GOP_ADD, GOP_DBL, GOP_MIXED_ADD, GOP_NEG, GOP_NORMALIZE = range(5)
 NTT_FFT, NTT_IFFT, NTT_COSET_FFT, NTT_ICOSET_FFT, NTT_DIV_Z_ON_COSET = range(5)
 DOMAIN_BASIC_RADIX2, DOMAIN_EXTENDED_RADIX2, DOMAIN_STEP_RADIX2 = 1, 2, 3
-ERR_CUDA, ERR_ARG, ERR_DOMAIN, ERR_UNSAT = -1, -2, -3, -4
+OK, ERR_CUDA, ERR_ARG, ERR_DOMAIN, ERR_UNSAT = 0, -1, -2, -3, -4
 
 # every symbol include/zkb.h declares: (name, restype, argtypes)
 _vp, _sz, _i, _u64p = C.c_void_p, C.c_size_t, C.c_int, C.c_void_p
@@ -46,6 +46,7 @@ SYMBOLS = {
     "zkb_group_sum": (_i, [_vp, _i, _u64p, _sz, _u64p]),
     "zkb_points_decompress": (_i, [_vp, _i, _u64p, _vp, _sz, _u64p, _vp]),
     "zkb_bases_upload": (_i, [_vp, _i, _u64p, _sz, _i, _i, C.POINTER(_vp)]),
+    "zkb_bases_synthetic": (_i, [_vp, _sz, C.c_uint64, _i, _i, C.POINTER(_vp)]),
     "zkb_bases_free": (None, [_vp]),
     "zkb_bases_device_bytes": (_sz, [_vp]),
     "zkb_msm": (_i, [_vp, _vp, _sz, _u64p, _sz, _u64p]),
@@ -305,6 +306,12 @@ class Context:
         self._chk(self.lib.zkb_bases_upload(self.h, group, a.ctypes.data, a.size // w, window_bits,
                                             precompute_factor, C.byref(h)))
         return Bases(self, h, group, a.size // w)
+
+    def synthetic_bases(self, n: int, seed: int = 1, window_bits: int = 0, precompute_factor: int = 0) -> "Bases":
+        """n distinct G1 bases made on the device (bench support, zkb_bases_synthetic)"""
+        h = C.c_void_p()
+        self._chk(self.lib.zkb_bases_synthetic(self.h, n, seed, window_bits, precompute_factor, C.byref(h)))
+        return Bases(self, h, G1, n)
 
     def msm(self, bases: "Bases", scalars, offset: int = 0) -> np.ndarray:
         s = _arr(scalars, 4)

@@ -36,6 +36,12 @@ _SIG = {
     "zkbr_batch_with_tampered": (_i, [_vp, _sz, _u64, _sz, C.POINTER(_i)]),
     "zkbr_cold_prove": (_i, [_vp, _u64, _vp]),
     "zkb_libsnark_devices": (_i, []),
+    "zkbr_synth_sha_chain": (_vp, [_sz, _u64]),
+    "zkbr_synth_free": (None, [_vp]),
+    "zkbr_synth_dims": (None, [_vp, _vp]),
+    "zkbr_synth_csr": (None, [_vp, _i, _vp, _vp, _vp]),
+    "zkbr_synth_witness": (None, [_vp, _vp]),
+    "zkbr_generators": (None, [_vp, _vp]),
 }
 _lib = None
 
@@ -150,3 +156,42 @@ def setup_roundtrip(payloads: int = 1, seed: int = 1, stock_prover: bool = False
     t = (C.c_double * 3)()
     rc = int(lib().zkbr_setup_roundtrip(payloads, seed, 1 if stock_prover else 0, t))
     return rc, t[0], t[1], t[2]
+
+
+def sha_chain(blocks: int, seed: int = 1):
+    """BASELINE config #5: `blocks` chained libsnark SHA-256 compression gadgets with a satisfying assignment.
+    Returns (constraint system as the dict zkb setup / key upload take, witness num_variables x 4)."""
+    L = lib()
+    h = L.zkbr_synth_sha_chain(blocks, seed)
+    if not h:
+        raise ZkbError(-1, "sha chain generation failed")
+    try:
+        d = (C.c_size_t * 6)()
+        L.zkbr_synth_dims(h, d)
+        nc, nv, ni = int(d[0]), int(d[1]), int(d[2])
+        cs = {"num_constraints": nc, "num_variables": nv, "num_inputs": ni}
+        for which, name in enumerate("ABC"):
+            nnz = int(d[3 + which])
+            rp = np.zeros(nc + 1, dtype=np.uint64)
+            col = np.zeros(max(nnz, 1), dtype=np.uint32)
+            co = np.zeros((max(nnz, 1), 4), dtype=np.uint64)
+            L.zkbr_synth_csr(h, which, rp.ctypes.data, col.ctypes.data, co.ctypes.data)
+            cs["csr_" + name] = (rp, col[:nnz], co[:nnz])
+        w = np.zeros((nv, 4), dtype=np.uint64)
+        L.zkbr_synth_witness(h, w.ctypes.data)
+        return cs, w
+    finally:
+        L.zkbr_synth_free(h)
+
+
+def generators():
+    """(G1 generator 12 limbs, G2 generator 24 limbs), Jacobian, Montgomery"""
+    g1, g2 = np.zeros(12, dtype=np.uint64), np.zeros(24, dtype=np.uint64)
+    lib().zkbr_generators(g1.ctypes.data, g2.ctypes.data)
+    return g1, g2
+
+
+def random_fr(count: int) -> np.ndarray:
+    out = np.zeros((count, 4), dtype=np.uint64)
+    lib().zkbr_random_fr(count, out.ctypes.data)
+    return out

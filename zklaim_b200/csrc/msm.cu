@@ -543,6 +543,32 @@ int zkb_bases_upload(zkb_ctx *ctx, int group, const uint64_t *affine, size_t n, 
     return ZKB_OK;
 }
 
+int zkb_bases_synthetic(zkb_ctx *ctx, size_t n, uint64_t seed, int window_bits, int precompute_factor, zkb_bases **out)
+{
+    if (!ctx || !out || n == 0) return fail(ctx, ZKB_ERR_ARG, "zkb_bases_synthetic: bad argument");
+    if (window_bits < 0 || window_bits > MSM_MAX_C || window_bits == 1 || precompute_factor < 0)
+        return fail(ctx, ZKB_ERR_ARG, "zkb_bases_synthetic: window_bits must be 0 or 2..20");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    zkb_bases *b = new zkb_bases();
+    b->plan.group = ZKB_G1;
+    b->n = n;
+    const int c = window_bits ? window_bits : msm_choose_c(n, ZKB_G1, precompute_factor);
+    Affine<Fq> gen; // G1 generator (1, 2), alt_bn128_init.cpp:148-150
+    gen.x = Fq::one();
+    gen.y = Fq::one() + Fq::one();
+    int rc = plan_add_job(ctx, &b->plan, n, c, precompute_factor);
+    if (!rc) rc = plan_alloc(ctx, &b->plan);
+    if (!rc) rc = plan_synth_job<Fq>(ctx, &b->plan, 0, gen, seed);
+    if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(ctx, ZKB_ERR_CUDA, "zkb_bases_synthetic: generation failed");
+    if (rc) {
+        plan_free(&b->plan);
+        delete b;
+        return rc;
+    }
+    *out = b;
+    return ZKB_OK;
+}
+
 void zkb_bases_free(zkb_bases *b)
 {
     if (!b) return;

@@ -375,6 +375,51 @@ k_next_copy(const Affine<F> *__restrict__ prev, Affine<F> *__restrict__ next, si
     st_vec(next + i, r);
 }
 
+// ---- measurement support: n distinct bases k_i * G made on the device (zkb_bases_synthetic) -------------------------
+// k_i = 252 bits of a counter-based hash of (seed, i); double-and-add as curve_utils.tcc:13-34, affine-normalised.
+__device__ __forceinline__ uint64_t synth_mix(uint64_t x)
+{
+    x += 0x9e3779b97f4a7c15ull;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+    return x ^ (x >> 31);
+}
+template <class F>
+__global__ void __launch_bounds__(128)
+k_synth_bases(Affine<F> gen, uint64_t seed, size_t n, Affine<F> *__restrict__ out)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t k[8];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const uint64_t v = synth_mix(seed * 0x100000001b3ull + 4 * i + j);
+        k[2 * j] = (uint32_t)v;
+        k[2 * j + 1] = (uint32_t)(v >> 32);
+    }
+    k[7] &= 0x0fffffffu;
+    k[0] |= 1u; // never zero
+    const XYZZ<F> x = scalar_mul<F>(k, XYZZ<F>::from_affine(gen));
+    Affine<F> r;
+    const F inv = (x.ZZ * x.ZZZ).inverse();
+    r.x = x.X * (inv * x.ZZZ);
+    r.y = x.Y * (inv * x.ZZ);
+    st_vec(out + i, r);
+}
+template <class F> int plan_synth_job(zkb_ctx *ctx, MsmPlan *plan, int job, const Affine<F> &gen, uint64_t seed)
+{
+    const MsmJob &J = plan->tab.j[job];
+    const size_t n = J.n_total;
+    Affine<F> *p = (Affine<F> *)plan->d_pts + J.pts_off;
+    k_synth_bases<F><<<ceil_div(n, 128), 128, 0, ctx->stream>>>(gen, seed, n, p);
+    ZKB_LAUNCH_CHECK(ctx);
+    for (int q = 1; q < J.F; q++) {
+        k_next_copy<F><<<ceil_div(n, 128), 128, 0, ctx->stream>>>(p + (size_t)(q - 1) * n, p + (size_t)q * n, n, J.G * J.c);
+        ZKB_LAUNCH_CHECK(ctx);
+    }
+    return ZKB_OK;
+}
+
 template <class F>
 int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t rmax, XYZZ<F> *d_res)
 {

@@ -60,6 +60,7 @@ int launch_accumulate(zkb_ctx *ctx, const Affine<F> *pts, const uint32_t *ent, c
 template <class F>
 int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, uint32_t rmax, XYZZ<F> *d_res);
 template <class F> int plan_upload_job(zkb_ctx *ctx, MsmPlan *plan, int job, const uint64_t *affine, bool from_device = false);
+template <class F> int plan_synth_job(zkb_ctx *ctx, MsmPlan *plan, int job, const Affine<F> &gen, uint64_t seed);
 template <class F> int results_to_host(zkb_ctx *ctx, const XYZZ<F> *d_res, size_t count, uint64_t *out_jacobian);
 
 // the whole pipeline: plain scalars (device, `zstride` words between proofs) -> d_res[batch][njobs]
