@@ -364,20 +364,28 @@ def extra_sharded(ctx, np, torch, dist, zk, bridge, rank, world, local, imad_pea
     key.tune(w)
     del kd
     wp = torch.from_numpy(w.view(np.int64)).pin_memory().numpy().view(np.uint64)  # pinned: the 124 MB travel at PCIe speed
-    best, best_dev = 1e9, 1e9
-    proof = None
-    for it in range(4):
-        dist.barrier()
-        torch.cuda.synchronize()
-        t = time.perf_counter()
-        proof = sharding.sharded_prove(ctx, key, wp, rnd[5], rnd[6], device=f"cuda:{local}")
-        best = min(best, tmax(1e3 * (time.perf_counter() - t)))
-        best_dev = min(best_dev, tmax(ctx.last_device_ms()))
-    same = torch.from_numpy(proof.view(np.int64).copy()).cuda()
-    ref0 = same.clone()
-    dist.broadcast(ref0, 0)
-    out["s22_one_proof"] = {"ms_device": best_dev, "ms_wall": best, "same_proof_on_every_rank": bool(torch.equal(same, ref0)),
-                            "key_shard_device_gb": key.device_bytes() / 1e9}
+    def one_proof(fn):
+        best, best_dev, proof = 1e9, 1e9, None
+        for it in range(4):
+            dist.barrier()
+            torch.cuda.synchronize()
+            t = time.perf_counter()
+            proof = fn()
+            best = min(best, tmax(1e3 * (time.perf_counter() - t)))
+            best_dev = min(best_dev, tmax(ctx.last_device_ms()))
+        mine = torch.from_numpy(proof.view(np.int64).copy()).cuda()
+        ref0 = mine.clone()
+        dist.broadcast(ref0, 0)
+        return best, best_dev, proof, bool(torch.equal(mine, ref0))
+
+    wall_r, dev_r, proof_r, same_r = one_proof(lambda: sharding.sharded_prove(ctx, key, wp, rnd[5], rnd[6], device=f"cuda:{local}"))
+    out["s22_one_proof_replicated_witness_map"] = {"ms_device": dev_r, "ms_wall": wall_r, "same_proof_on_every_rank": same_r}
+    wall_s, dev_s, proof_s, same_s = one_proof(lambda: sharding.sharded_prove_split(ctx, key, wp, rnd[5], rnd[6], device=f"cuda:{local}"))
+    out["s22_one_proof"] = {"ms_device": dev_s, "ms_wall": wall_s, "same_proof_on_every_rank": same_s,
+                            "equals_replicated_form": bool(np.array_equal(proof_r, proof_s)),
+                            "key_shard_device_gb": key.device_bytes() / 1e9,
+                            "form": "witness map split by polynomial over ranks 0-2 (world >= 3; else replicated), H broadcast; "
+                                    "ms_device = max over ranks of the library's CUDA-event time (NCCL exchanges are in ms_wall only)"}
     key.free()
     return out
 
@@ -497,6 +505,18 @@ def run_ours(args):
 
     imad_peak = ctx.imad_peak(1024)
     extras = {}
+    if world == 1 and not args.no_extras:
+        # the zklaim-facing entry point: credentials in, proofs out (host witness generation by zklaim's gadget code on all
+        # host threads + GPU); two caller threads, so that one batch's witnesses are generated while another is on the GPU
+        try:
+            with stdout_to_stderr():
+                cred.stream(1, BATCH, 2)  # warm
+                n_z, sec_z = cred.stream(4, BATCH, 2)
+            extras["e2e_zklaim"] = {"value": n_z / sec_z, "unit": "proofs/s", "api": "zkb_libsnark_prove_batch (bridge), 2 caller threads x 4 batches of 64 credentials",
+                                    "host_threads": int(os.environ.get("OMP_NUM_THREADS", 0)) or len(os.sched_getaffinity(0)),
+                                    "note": "bounded by the host: zklaim's gadget code needs ~10 ms per credential and core for the witness"}
+        except Exception as e:
+            extras["e2e_zklaim"] = {"error": repr(e)}
     if not args.no_extras:
         import zklaim_b200 as zk_mod
         if world > 1:

@@ -23,6 +23,7 @@
 #include "zklaim/libsnark_wrapper.cpp" /* the reference bridge, unchanged */
 
 #include <chrono>
+#include <thread>
 #include <fcntl.h>
 #include <openssl/sha.h>
 
@@ -158,13 +159,30 @@ bool build_witness(zklaim_ctx *ctx, std::vector<FrT> &primary, std::vector<FrT> 
 }
 
 struct StdoutMute { /* what libsnark_wrapper.cpp:221-226 / :245-246 do around every call: the gadget prints to stdout */
-    int saved;
+    /* several host threads may be inside the bridge at once: the first one in redirects, the last one out restores */
+    static std::mutex &mu()
+    {
+        static std::mutex m;
+        return m;
+    }
+    static int &depth()
+    {
+        static int d = 0;
+        return d;
+    }
+    static int &saved()
+    {
+        static int fd = -1;
+        return fd;
+    }
     StdoutMute()
     {
+        std::lock_guard<std::mutex> g(mu());
+        if (depth()++) return;
         libff::inhibit_profiling_counters = 1;
         libff::inhibit_profiling_info = 1;
         fflush(stdout);
-        saved = dup(STDOUT_FILENO);
+        saved() = dup(STDOUT_FILENO);
         /* the reference close()s fd 1; pointing it at /dev/null silences the same output without leaving descriptor 1
          * free for whoever opens a file next (CUDA, a profiler, another thread), who would then lose it on restore */
         const int nul = open("/dev/null", O_WRONLY);
@@ -176,11 +194,14 @@ struct StdoutMute { /* what libsnark_wrapper.cpp:221-226 / :245-246 do around ev
     }
     ~StdoutMute()
     {
+        std::lock_guard<std::mutex> g(mu());
+        if (--depth()) return;
         fflush(stdout);
         std::cout.clear();
-        if (saved >= 0) {
-            dup2(saved, STDOUT_FILENO);
-            close(saved);
+        if (saved() >= 0) {
+            dup2(saved(), STDOUT_FILENO);
+            close(saved());
+            saved() = -1;
         }
     }
 };
@@ -612,6 +633,60 @@ int zkbr_verify_roundtrip(void *h, size_t count, uint64_t seed0, size_t tamper, 
         *accepted += gpu_res[i] == 0 ? 1 : 0;
     }
     return agree;
+}
+
+/* The zklaim-facing throughput: `threads` host threads, each proving `batches` batches of
+ * `batch` fresh credentials through zkb_libsnark_prove_batch.  The entry point is thread-safe: the witness generation of
+ * one caller (zklaim's gadget code, all OpenMP threads) overlaps the GPU phase of another, which is how a service keeps
+ * the device fed.  Returns the credentials proved (every one checked to have a proof; the last batch of thread 0 is run
+ * through the reference's libsnark_verify), < 0 on failure; seconds[0] = wall time of the whole stream. */
+int zkbr_stream(void *h, size_t batches, size_t batch, int threads, uint64_t seed0, double *seconds)
+{
+    Bench *b = (Bench *)h;
+    if (threads < 1) threads = 1;
+    std::vector<int> rc(threads, 0);
+    std::vector<size_t> proved(threads, 0);
+    std::vector<std::unique_ptr<Credential>> kept; /* the last batch of thread 0: verified after the clock stops */
+    auto body = [&](int t) {
+        for (size_t k = 0; k < batches && rc[t] == 0; k++) {
+            std::vector<std::unique_ptr<Credential>> creds;
+            std::vector<zklaim_ctx *> ptrs;
+            for (size_t i = 0; i < batch; i++) {
+                creds.emplace_back(new Credential(b->payloads, seed0 + ((uint64_t)t << 32) + k * batch + i));
+                zklaim_ctx &c = creds.back()->ctx;
+                /* the callers share the issuer's key buffer (same address: hashed once) */
+                c.pk = b->issuer->ctx.pk;
+                c.pk_size = b->issuer->ctx.pk_size;
+                ptrs.push_back(&c);
+            }
+            int r = zkb_libsnark_prove_batch(ptrs.data(), batch);
+            for (size_t i = 0; i < batch && r == 0; i++)
+                if (!ptrs[i]->proof) r = -5;
+            for (auto &c : creds) c->ctx.pk = NULL; /* not owned */
+            rc[t] = r;
+            if (r == 0) proved[t] += batch;
+            if (r == 0 && t == 0 && k + 1 == batches) kept = std::move(creds);
+        }
+    };
+    const double t0 = now_s();
+    std::vector<std::thread> th;
+    for (int t = 1; t < threads; t++) th.emplace_back(body, t);
+    body(0);
+    for (auto &x : th) x.join();
+    seconds[0] = now_s() - t0;
+    size_t total = 0;
+    for (int t = 0; t < threads; t++) {
+        if (rc[t]) return rc[t] < 0 ? rc[t] : -rc[t];
+        total += proved[t];
+    }
+    for (auto &c : kept) { /* the reference's verifier on what the stream produced */
+        c->ctx.vk = b->issuer->ctx.vk;
+        c->ctx.vk_size = b->issuer->ctx.vk_size;
+        const int v = libsnark_verify(&c->ctx);
+        c->ctx.vk = NULL;
+        if (v != 0) return -6;
+    }
+    return (int)total;
 }
 
 /* `count` credentials of which credential `tamper` has a flipped hash byte, through zkb_libsnark_prove_batch_ex: the

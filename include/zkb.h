@@ -218,6 +218,23 @@ int zkb_prove_partial(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const
 int zkb_prove_combine(zkb_ctx *ctx, const zkb_partial *parts, size_t n, const uint64_t r[4], const uint64_t s[4],
                       zkb_proof *out);
 
+/* The same with the witness map SPLIT by polynomial instead of replicated (r1cs_to_qap.tcc:240-293 treats A, B and C
+ * alike: SpMV, iFFT, coset FFT -- three independent chains).  Three shards run one chain each, one shard divides and
+ * transforms back, every shard receives the H coefficients; the exchanges (two m x 32-byte vectors in, one out) are
+ * the caller's -- NCCL send / recv / broadcast in zklaim_b200/sharding.py, peer copies in a single process:
+ *   _begin   uploads w, r, s, starts the shard's witness-only sums (A, B-in-G1, B-in-G2 ranges) on side streams and, for
+ *            which = 0 / 1 / 2, writes the coset evaluations of polynomial A / B / C to d_part (device, m x 4 limbs);
+ *            which = -1: no chain.  check != 0: this shard also evaluates all three products and tests
+ *            <a,z><b,z> = <c,z> per constraint (its _end then reports ZKB_ERR_UNSAT); one shard should do so.
+ *   _combine d_abc = [A' | B' | C'] on the coset (device, 3 m x 4 limbs, destroyed) -> H coefficients as plain integers
+ *            at d_H_plain (device, m x 4 limbs): (A' B' - C') / Z, inverse coset transform (:270-311).
+ *   _end     H (device, plain) -> the shard's share of the H + L sum; joins the side lanes; writes the partial.
+ * One proof in flight per context.  zkb_last_device_ms() after _end = the device time of the three calls. */
+int zkb_prove_split_begin(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4], int which,
+                          int check, void *d_part);
+int zkb_prove_split_combine(zkb_ctx *ctx, const zkb_key *key, void *d_abc, void *d_H_plain);
+int zkb_prove_split_end(zkb_ctx *ctx, const zkb_key *key, const void *d_H_plain, zkb_partial *out);
+
 /* `count` independent proofs under one key; w, r, s, out are arrays of `count` items
  * (w: count x num_variables x 4).  The batch is pipelined on the context's device. */
 int zkb_prove_batch(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w, const uint64_t *r,

@@ -312,3 +312,48 @@ def test_witness_map_at_scale_bit_exact(zctx, ref, nc, kind):
         assert e.value.code == zk.ERR_UNSAT
     key.free()
     circ.free()
+
+
+@pytest.mark.parametrize("world", [3, 5])
+def test_one_proof_with_the_witness_map_split_by_polynomial(zctx, ref, world):
+    """SURVEY 8(e) optional row: ranks 0 / 1 / 2 compute the coset evaluations of A / B / C (zkb_prove_split_begin), one
+    rank divides and transforms back (zkb_prove_split_combine), every rank finishes its share from the H coefficients
+    (zkb_prove_split_end).  One GPU plays every rank (a context per rank, device buffers through torch): the proof bytes
+    equal the reference's, on the zklaim circuit and on a step-domain example; the checking rank reports an
+    unsatisfying witness."""
+    import torch
+    for circ in (ref.Circuit.zklaim(1, 1), ref.Circuit.example(2048 + 256 - 11, 10, seed=9)):
+        circ.setup()
+        kd = circ.export_key()
+        w = circ.witness()
+        r, s = ref.sha512_rng(51, 1)[0], ref.sha512_rng(52, 1)[0]
+        exp = circ.prove(w, r, s, want_H=False)
+        m = circ.dims()["m"]
+        for witness, unsat in ((w, False), (None, True)):
+            if unsat:
+                witness = w.copy()
+                witness[circ.dims()["num_inputs"] + 3] = ref.sha512_rng(7, 1)[0]
+            ctxs = [zk.Context(0) for _ in range(world)]
+            keys = [ctxs[k].upload_key(kd, k, world) for k in range(world)]
+            abc = torch.empty((3, m, 4), dtype=torch.int64, device="cuda")
+            H = torch.empty((m, 4), dtype=torch.int64, device="cuda")
+            for k in range(world):
+                ctxs[k].prove_split_begin(keys[k], witness, r, s, k if k < 3 else -1, check=(k == world - 1),
+                                          d_part=abc[k].data_ptr() if k < 3 else 0)
+            ctxs[0].prove_split_combine(keys[0], abc.data_ptr(), H.data_ptr())
+            parts, failed = [], 0
+            for k in range(world):
+                try:
+                    parts.append(ctxs[k].prove_split_end(keys[k], H.data_ptr()))
+                except zk.ZkbError as e:
+                    assert e.code == zk.ERR_UNSAT and k == world - 1
+                    failed += 1
+            if unsat:
+                assert failed == 1
+            else:
+                got = ctxs[0].prove_combine(np.stack(parts), r, s)
+                assert ref.proof_bytes(got) == ref.proof_bytes(exp["proof"])
+            for k in range(world):
+                keys[k].free()
+                ctxs[k].close()
+        circ.free()

@@ -110,3 +110,71 @@ def test_sharded_msm_world_size_n_gloo(tmp_path, world, n, n2):
         outs.append(out)
     for r, (p, out) in enumerate(zip(procs, outs)):
         assert p.returncode == 0 and f"RANK {r} OK" in out, out
+
+
+SPLIT_WORKER = r"""
+import ctypes, sys
+import numpy as np
+sys.path.insert(0, {root!r})
+import torch.distributed as dist
+from zklaim_b200 import sharding
+
+M = 64
+def view(ptr, n):                        # the "device" buffers are host tensors under gloo
+    return np.ctypeslib.as_array(ctypes.cast(ptr, ctypes.POINTER(ctypes.c_uint64)), shape=(n,))
+
+class FakeKey:
+    def domain(self): return (M, 1)
+
+class FakeDevice:                        # records the data flow of zkb_prove_split_* instead of doing arithmetic
+    def __init__(self, rank): self.rank = rank; self.checked = False
+    def prove_split_begin(self, key, w, r, s, which, check, d_part=0):
+        self.checked = check
+        assert (which >= 0) == (d_part != 0)
+        if which >= 0: view(d_part, M * 4)[:] = 1000 * (which + 1) + np.arange(M * 4, dtype=np.uint64)
+    def prove_split_combine(self, key, d_abc, d_H):
+        abc = view(d_abc, 3 * M * 4).reshape(3, M * 4)
+        for k in range(3): assert abc[k][0] == 1000 * (k + 1) and abc[k][5] == 1000 * (k + 1) + 5, abc[k][:8]
+        view(d_H, M * 4)[:] = abc[0] + 2 * abc[1] + 3 * abc[2]
+    def prove_split_end(self, key, d_H):
+        out = np.zeros(60, dtype=np.uint64)
+        out[0], out[1] = self.rank, view(d_H, M * 4).sum()
+        return out
+    def prove_combine(self, parts, r, s): return parts
+    def prove_partial(self, key, w, r, s): raise AssertionError("the split form was expected")
+
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:{port}", rank=int(sys.argv[1]), world_size={world})
+rank, world = dist.get_rank(), dist.get_world_size()
+dev = FakeDevice(rank)
+z = np.zeros((4, 4), dtype=np.uint64)
+parts = sharding.sharded_prove_split(dev, FakeKey(), z, z[0], z[0])
+want_H = sum((k + 1) * (1000 * (k + 1) * M * 4 + (M * 4) * (M * 4 - 1) // 2) for k in range(3))
+ok = parts.shape == (world, 60) and [int(x) for x in parts[:, 0]] == list(range(world)) and all(int(x) == want_H for x in parts[:, 1])
+ok = ok and dev.checked == (rank == world - 1)
+dist.barrier()
+dist.destroy_process_group()
+print("RANK", rank, "OK" if ok else "MISMATCH", flush=True)
+sys.exit(0 if ok else 1)
+"""
+
+
+@pytest.mark.parametrize("world", [3, 4])
+def test_split_witness_map_orchestration_gloo(tmp_path, world):
+    """sharding.sharded_prove_split over gloo with a device that records the data flow: ranks 0 / 1 / 2 produce the three
+    coset vectors, rank 0 receives the other two in order and combines, every rank receives the same H and contributes its
+    share in rank order; only the last rank is asked to check satisfiability."""
+    script = tmp_path / "split_worker.py"
+    script.write_text(SPLIT_WORKER.format(root=ROOT, port=_free_port(), world=world))
+    procs = [subprocess.Popen([sys.executable, str(script), str(r)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+             for r in range(world)]
+    outs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=120)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        outs.append(out)
+    for r, (p, out) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0 and f"RANK {r} OK" in out, out

@@ -78,6 +78,9 @@ SYMBOLS = {
     "zkb_key_upload_shard": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
     "zkb_prove_partial": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _u64p, _u64p]),
     "zkb_prove_combine": (_i, [_vp, _u64p, _sz, _u64p, _u64p, _vp]),
+    "zkb_prove_split_begin": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _i, _i, _vp]),
+    "zkb_prove_split_combine": (_i, [_vp, _vp, _vp, _vp]),
+    "zkb_prove_split_end": (_i, [_vp, _vp, _vp, _u64p]),
     "zkb_key_tune": (_i, [_vp, _vp, _u64p]),
     "zkb_key_windows": (_i, [_vp, C.POINTER(_i)]),
     "zkb_setup": (_i, [_vp, _vp, _vp, C.POINTER(_i)]),
@@ -392,6 +395,20 @@ class Context:
         w, r, s = _arr(w, 4), _arr(r, 4), _arr(s, 4)
         out = np.zeros(60, dtype=np.uint64)
         self._chk(self.lib.zkb_prove_partial(self.h, key.h, w.ctypes.data, r.ctypes.data, s.ctypes.data, out.ctypes.data, None))
+        return out
+
+    def prove_split_begin(self, key: "Key", w, r, s, which: int, check: bool, d_part: int = 0) -> None:
+        """zkb_prove_split_begin: d_part = CUDA device pointer (m x 4 limbs) when which in (0, 1, 2)"""
+        w, r, s = _arr(w, 4), _arr(r, 4), _arr(s, 4)
+        self._chk(self.lib.zkb_prove_split_begin(self.h, key.h, w.ctypes.data, r.ctypes.data, s.ctypes.data, which, 1 if check else 0,
+                                                 C.c_void_p(d_part)))
+
+    def prove_split_combine(self, key: "Key", d_abc: int, d_H: int) -> None:
+        self._chk(self.lib.zkb_prove_split_combine(self.h, key.h, C.c_void_p(d_abc), C.c_void_p(d_H)))
+
+    def prove_split_end(self, key: "Key", d_H: int) -> np.ndarray:
+        out = np.zeros(60, dtype=np.uint64)
+        self._chk(self.lib.zkb_prove_split_end(self.h, key.h, C.c_void_p(d_H), out.ctypes.data))
         return out
 
     def prove_combine(self, parts, r, s) -> np.ndarray:

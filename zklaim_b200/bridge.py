@@ -33,6 +33,7 @@ _SIG = {
     "zkbr_prove_tampered": (_i, [_vp, _u64]),
     "zkbr_setup_roundtrip": (_i, [_sz, _u64, _i, _vp]),
     "zkbr_import_check": (_i, [_vp, _vp]),
+    "zkbr_stream": (_i, [_vp, _sz, _sz, _i, _u64, _vp]),
     "zkbr_batch_with_tampered": (_i, [_vp, _sz, _u64, _sz, C.POINTER(_i)]),
     "zkbr_cold_prove": (_i, [_vp, _u64, _vp]),
     "zkb_libsnark_devices": (_i, []),
@@ -125,6 +126,15 @@ class Credentials:
         rc = C.c_int(0)
         good = int(self.L.zkbr_batch_with_tampered(self.h, count, seed0, tamper, C.byref(rc)))
         return good, rc.value
+
+    def stream(self, batches: int, batch: int = 64, threads: int = 2, seed0: int = 70000):
+        """`threads` host threads x `batches` batches of `batch` credentials through zkb_libsnark_prove_batch (host witness
+        generation by zklaim's gadget code + GPU).  Returns (credentials proved, wall seconds)."""
+        t = (C.c_double * 1)()
+        n = int(self.L.zkbr_stream(self.h, batches, batch, threads, seed0, t))
+        if n < 0:
+            raise ZkbError(n, "zkbr_stream failed")
+        return n, t[0]
 
     def import_check(self):
         """the issuer's serialised proving key through the reference importer and through the deferred (GPU) importer.

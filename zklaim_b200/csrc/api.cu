@@ -110,7 +110,8 @@ int zkb_init(int device_id, zkb_ctx **out)
         cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_join[0], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_join[1], cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev2) != cudaSuccess || cudaEventCreate(&ctx->ev3) != cudaSuccess) {
         delete ctx;
         return fail(nullptr, ZKB_ERR_CUDA, "zkb_init: stream/event creation failed");
     }
@@ -138,6 +139,8 @@ void zkb_shutdown(zkb_ctx *ctx)
             for (int k = 0; k < 2; k++) cudaEventDestroy(ctx->pe[g][k]);
     }
     cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev2);
+    cudaEventDestroy(ctx->ev3);
     cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->ev_fork);
     cudaEventDestroy(ctx->ev_join[0]);

@@ -48,6 +48,7 @@ struct zkb_ctx {
     uint32_t func_attr_done = 0;            // cudaFuncSetAttribute calls already made on this device (bit per kernel)
     int lane_bias = 0;                      // scratch-slot offset of the active MSM lane
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev2 = nullptr, ev3 = nullptr; // second pair: the later phases of a split proof
     // pipelined batches (zkb_prove_batch_submit / _collect): inputs of the next batch travel on copy_stream into one of
     // two staging slots while the current batch computes
     cudaStream_t copy_stream = nullptr;

@@ -99,9 +99,9 @@ __device__ __forceinline__ Fr spmv_term(const CsrDev &csr, int mat, const Fr *__
 }
 __global__ void __launch_bounds__(128)
 k_spmv(CsrDev csr, uint32_t long_blocks, const Fr *__restrict__ Z, size_t zlen, size_t nc, size_t ni, size_t m, int batch,
-       Fr *__restrict__ abc)
+       Fr *__restrict__ abc, int mat_base)
 {
-    const int mat = blockIdx.y, p = blockIdx.z;
+    const int mat = blockIdx.y + mat_base, p = blockIdx.z;
     const Fr *z = Z + (size_t)p * zlen;
     Fr *out = abc + ((size_t)mat * batch + p) * m;
     const uint32_t nlong = csr.nlong[mat];
@@ -689,6 +689,37 @@ int chunk_size(const zkb_key *key, size_t count)
     return c ? (int)c : 1;
 }
 
+// abc[(mat * batch + p) * m + row] = <row of matrix mat, z_p> for the matrices mat_lo .. mat_lo + nmat - 1 (stage 1)
+int spmv_stage(zkb_ctx *ctx, const zkb_key *key, int batch, Fr *abc, int mat_lo, int nmat)
+{
+    cudaStream_t st = ctx->stream;
+    const size_t m = key->m;
+    Fr *Z = ctx->scratch[SP_Z].as<Fr>();
+    CsrDev csr;
+    for (int k = 0; k < 3; k++) {
+        csr.rowptr[k] = key->rowptr[k];
+        csr.col[k] = key->col[k];
+        csr.coeff[k] = key->coeff[k];
+        csr.perm[k] = key->rowperm[k];
+        csr.nlong[k] = key->nlong[k];
+        csr.ngiant[k] = key->ngiant[k];
+    }
+    if (key->n_giant_row) { // the few giant rows of all three matrices (cheap: done whatever the subset)
+        ZKB_CUDA(ctx, ctx->scratch[SP_GIANT].ensure((size_t)batch * key->n_giant_seg * sizeof(Fr)));
+        Fr *partial = ctx->scratch[SP_GIANT].as<Fr>();
+        k_spmv_giant<<<dim3(key->n_giant_seg, batch), 128, 0, st>>>(csr, key->giant_seg, Z, key->zlen, key->n_giant_seg, partial);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_spmv_giant_finish<<<dim3(key->n_giant_row, batch), 32, 0, st>>>(key->giant_row, partial, key->n_giant_seg, m, batch, abc);
+        ZKB_LAUNCH_CHECK(ctx);
+    }
+    uint32_t nl = 0;
+    for (int k = mat_lo; k < mat_lo + nmat; k++) nl = std::max(nl, key->nlong[k]);
+    const uint32_t long_blocks = (nl + 3) / 4;
+    k_spmv<<<dim3(long_blocks + ceil_div(m, 128), nmat, batch), 128, 0, st>>>(csr, long_blocks, Z, key->zlen, key->nc, key->ni, m, batch, abc, mat_lo);
+    ZKB_LAUNCH_CHECK(ctx);
+    return ZKB_OK;
+}
+
 // Z rows for `batch` proofs are in place (w, r, s uploaded); runs stages 1-2.  Leaves H in Z and P.
 int witness_map_chunk(zkb_ctx *ctx, const zkb_key *key, int batch, uint32_t *d_flags)
 {
@@ -702,31 +733,13 @@ int witness_map_chunk(zkb_ctx *ctx, const zkb_key *key, int batch, uint32_t *d_f
         ZKB_CUDA(ctx, ctx->scratch[SP_TMP].ensure((size_t)3 * batch * m * sizeof(Fr)));
         tmp = ctx->scratch[SP_TMP].as<Fr>();
     }
-    CsrDev csr;
-    for (int k = 0; k < 3; k++) {
-        csr.rowptr[k] = key->rowptr[k];
-        csr.col[k] = key->col[k];
-        csr.coeff[k] = key->coeff[k];
-        csr.perm[k] = key->rowperm[k];
-        csr.nlong[k] = key->nlong[k];
-        csr.ngiant[k] = key->ngiant[k];
-    }
-    if (key->n_giant_row) {
-        ZKB_CUDA(ctx, ctx->scratch[SP_GIANT].ensure((size_t)batch * key->n_giant_seg * sizeof(Fr)));
-        Fr *partial = ctx->scratch[SP_GIANT].as<Fr>();
-        k_spmv_giant<<<dim3(key->n_giant_seg, batch), 128, 0, st>>>(csr, key->giant_seg, Z, key->zlen, key->n_giant_seg, partial);
-        ZKB_LAUNCH_CHECK(ctx);
-        k_spmv_giant_finish<<<dim3(key->n_giant_row, batch), 32, 0, st>>>(key->giant_row, partial, key->n_giant_seg, m, batch, abc);
-        ZKB_LAUNCH_CHECK(ctx);
-    }
-    const uint32_t long_blocks = (std::max(key->nlong[0], std::max(key->nlong[1], key->nlong[2])) + 3) / 4;
-    k_spmv<<<dim3(long_blocks + ceil_div(m, 128), 3, batch), 128, 0, st>>>(csr, long_blocks, Z, key->zlen, key->nc, key->ni, m, batch, abc);
-    ZKB_LAUNCH_CHECK(ctx);
+    int rc = spmv_stage(ctx, key, batch, abc, 0, 3);
+    if (rc) return rc;
     if (key->nc) {
         k_sat_check<<<dim3(ceil_div(key->nc, 128), batch), 128, 0, st>>>(abc, key->nc, m, batch, d_flags);
         ZKB_LAUNCH_CHECK(ctx);
     }
-    int rc = domain_to_coset(ctx, &key->dom, abc, m, 3 * batch, tmp);
+    rc = domain_to_coset(ctx, &key->dom, abc, m, 3 * batch, tmp);
     if (rc) return rc;
     const bool basic = key->kind == ZKB_DOMAIN_BASIC_RADIX2;
     k_h_pointwise<<<dim3(ceil_div(m, 128), batch), 128, 0, st>>>(abc, m, batch, key->dom.zinv, basic ? nullptr : key->dom.zinv_tab);
@@ -1030,6 +1043,123 @@ int zkb_prove_combine(zkb_ctx *ctx, const zkb_partial *parts, size_t n, const ui
     ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_out, sizeof(zkb_proof), cudaMemcpyDeviceToHost, st));
     ZKB_CUDA(ctx, cudaStreamSynchronize(st));
     memcpy(out, ctx->pinned, sizeof(zkb_proof));
+    return ZKB_OK;
+}
+
+// ---- one proof over several GPUs with the witness map split by polynomial (optional row) ------
+int zkb_prove_split_begin(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4], int which,
+                          int check, void *d_part)
+{
+    if (!ctx || !key || !w || !r || !s || which < -1 || which > 2 || (which >= 0 && !d_part))
+        return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_begin: bad argument");
+    if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_begin: key lives on another device");
+    if (key->cs_only) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_begin: this key has no queries");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    cudaStream_t st = ctx->stream;
+    const size_t nv = key->nv, m = key->m, zlen = key->zlen;
+    ZKB_CUDA(ctx, ctx->scratch[SP_Z].ensure(zlen * sizeof(Fr)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_P].ensure(zlen * sizeof(Fr)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_RS].ensure(2 * sizeof(Fr)));
+    ZKB_CUDA(ctx, ctx->scratch[SP_FLAGS].ensure(4));
+    ZKB_CUDA(ctx, ctx->scratch[SP_PROOF].ensure(sizeof(zkb_partial)));
+    Fr *Z = ctx->scratch[SP_Z].as<Fr>();
+    Fr *rs = ctx->scratch[SP_RS].as<Fr>();
+    uint32_t *flags = ctx->scratch[SP_FLAGS].as<uint32_t>();
+    if (nv) ZKB_CUDA(ctx, cudaMemcpyAsync(Z + 1, w, nv * sizeof(Fr), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(rs, r, sizeof(Fr), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(rs + 1, s, sizeof(Fr), cudaMemcpyHostToDevice, st));
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+    int rc = stage_rows(ctx, key, 1, rs, flags);
+    if (!rc) rc = msm_side_lanes(ctx, key, 1, true);
+    if (!rc && (check || which >= 0)) {
+        ZKB_CUDA(ctx, ctx->scratch[SP_ABC].ensure((size_t)3 * m * sizeof(Fr)));
+        Fr *abc = ctx->scratch[SP_ABC].as<Fr>();
+        Fr *tmp = nullptr;
+        if (key->kind != ZKB_DOMAIN_BASIC_RADIX2) {
+            ZKB_CUDA(ctx, ctx->scratch[SP_TMP].ensure((size_t)3 * m * sizeof(Fr)));
+            tmp = ctx->scratch[SP_TMP].as<Fr>();
+        }
+        rc = check ? spmv_stage(ctx, key, 1, abc, 0, 3) : spmv_stage(ctx, key, 1, abc, which, 1);
+        if (!rc && check && key->nc) {
+            k_sat_check<<<dim3(ceil_div(key->nc, 128), 1), 128, 0, st>>>(abc, key->nc, m, 1, flags);
+            ZKB_LAUNCH_CHECK(ctx);
+        }
+        if (!rc && which >= 0) {
+            rc = domain_to_coset(ctx, &key->dom, abc + (size_t)which * m, m, 1, tmp);
+            if (!rc) ZKB_CUDA(ctx, cudaMemcpyAsync(d_part, abc + (size_t)which * m, m * sizeof(Fr), cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    if (rc) {
+        cudaDeviceSynchronize();
+        return rc;
+    }
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(st)); // d_part is complete; the side lanes may still be running
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_ms = ms;
+    return ZKB_OK;
+}
+
+int zkb_prove_split_combine(zkb_ctx *ctx, const zkb_key *key, void *d_abc, void *d_H_plain)
+{
+    if (!ctx || !key || !d_abc || !d_H_plain) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_combine: bad argument");
+    if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_combine: key lives on another device");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    cudaStream_t st = ctx->stream;
+    const size_t m = key->m;
+    Fr *abc = (Fr *)d_abc;
+    Fr *tmp = nullptr;
+    if (key->kind != ZKB_DOMAIN_BASIC_RADIX2) {
+        ZKB_CUDA(ctx, ctx->scratch[SP_TMP].ensure((size_t)3 * m * sizeof(Fr)));
+        tmp = ctx->scratch[SP_TMP].as<Fr>();
+    }
+    ZKB_CUDA(ctx, ctx->scratch[SP_W].ensure((m + 1) * sizeof(Fr))); // the Montgomery form of H is not needed downstream
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev2, st));
+    const bool basic = key->kind == ZKB_DOMAIN_BASIC_RADIX2;
+    k_h_pointwise<<<dim3(ceil_div(m, 128), 1), 128, 0, st>>>(abc, m, 1, key->dom.zinv, basic ? nullptr : key->dom.zinv_tab);
+    ZKB_LAUNCH_CHECK(ctx);
+    int rc = domain_h_from_coset(ctx, &key->dom, abc, m, 1, tmp, ctx->scratch[SP_W].as<Fr>(), (Fr *)d_H_plain, m);
+    if (rc) return rc;
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev3, st));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3);
+    ctx->last_ms += ms;
+    return ZKB_OK;
+}
+
+int zkb_prove_split_end(zkb_ctx *ctx, const zkb_key *key, const void *d_H_plain, zkb_partial *out)
+{
+    if (!ctx || !key || !d_H_plain || !out) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_end: bad argument");
+    if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_end: key lives on another device");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    cudaStream_t st = ctx->stream;
+    Fr *P = ctx->scratch[SP_P].as<Fr>();
+    uint32_t *flags = ctx->scratch[SP_FLAGS].as<uint32_t>();
+    zkb_proof *d_out = ctx->scratch[SP_PROOF].as<zkb_proof>();
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev2, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(P + key->z_h(), d_H_plain, key->m * sizeof(Fr), cudaMemcpyDeviceToDevice, st));
+    int rc = msm_main_lane_and_assemble(ctx, key, 1, d_out, (zkb_partial *)d_out);
+    if (rc) {
+        cudaDeviceSynchronize();
+        return rc;
+    }
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev3, st));
+    if (ensure_pinned(ctx, sizeof(zkb_partial) + 4)) return ZKB_ERR_CUDA;
+    uint32_t *h_flags = (uint32_t *)((char *)ctx->pinned + sizeof(zkb_partial));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d_out, sizeof(zkb_partial), cudaMemcpyDeviceToHost, st));
+    ZKB_CUDA(ctx, cudaMemcpyAsync(h_flags, flags, 4, cudaMemcpyDeviceToHost, st));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3);
+    ctx->last_ms += ms;
+    prof_collect(ctx);
+    memcpy(out, ctx->pinned, sizeof(zkb_partial));
+    if (*h_flags) {
+        memset(out, 0, sizeof(zkb_partial));
+        return fail(ctx, ZKB_ERR_UNSAT, "the witness does not satisfy the constraint system");
+    }
     return ZKB_OK;
 }
 

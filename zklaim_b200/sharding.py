@@ -79,3 +79,43 @@ def sharded_prove(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndarray, g
     part = ctx.prove_partial(key_shard, w, r, s)
     parts = gather_partials(part, group, device)
     return ctx.prove_combine(parts, r, s)
+
+
+def sharded_prove_split(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndarray, group=None, device: Optional[str] = None) -> np.ndarray:
+    """ONE Groth16 proof over all ranks with the witness map SPLIT by polynomial instead of replicated (needs >= 3 ranks;
+    fewer fall back to sharded_prove).  r1cs_to_qap_witness_map treats A, B and C alike (r1cs_to_qap.tcc:240-293): ranks
+    0 / 1 / 2 run SpMV + iFFT + coset FFT of one polynomial each (zkb_prove_split_begin), ranks 1 and 2 send their m x 32
+    bytes to rank 0 (NCCL send / recv), rank 0 divides by Z and transforms back (zkb_prove_split_combine), broadcasts the H
+    coefficients, and every rank computes its share of the H + L sum (zkb_prove_split_end); the witness-only sums run on
+    side streams from the start.  The last rank also checks satisfiability.  Exchanges: 2 x 32 m bytes in, 32 m bytes out."""
+    import torch
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 3:
+        return sharded_prove(ctx, key_shard, w, r, s, group, device)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = torch.device(device if device is not None else ("cuda" if dist.get_backend(group) == "nccl" else "cpu"))
+
+    def sync():  # the library works on its own streams and returns with its results complete; torch's stream carries NCCL
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+
+    m = key_shard.domain()[0]
+    which = rank if rank < 3 else -1
+    abc = torch.empty((3, m, 4), dtype=torch.int64, device=dev) if rank == 0 else None
+    part = abc[0] if rank == 0 else (torch.empty((m, 4), dtype=torch.int64, device=dev) if which >= 0 else None)
+    H = torch.empty((m, 4), dtype=torch.int64, device=dev)
+    sync()
+    ctx.prove_split_begin(key_shard, w, r, s, which, check=(rank == world - 1), d_part=part.data_ptr() if part is not None else 0)
+    if rank == 0:
+        dist.recv(abc[1], src=1, group=group)
+        dist.recv(abc[2], src=2, group=group)
+        sync()
+        ctx.prove_split_combine(key_shard, abc.data_ptr(), H.data_ptr())
+    elif rank in (1, 2):
+        dist.send(part, dst=0, group=group)
+    dist.broadcast(H, src=0, group=group)
+    sync()
+    share = ctx.prove_split_end(key_shard, H.data_ptr())
+    parts = gather_partials(share, group, device)
+    return ctx.prove_combine(parts, r, s)
