@@ -132,6 +132,22 @@ int zkb_domain_select(size_t min_size, size_t *m_out, int *kind_out);
 /* In-place domain operation on m = domain size elements of host memory. */
 int zkb_domain_op(zkb_ctx *ctx, size_t min_size, int op, uint64_t *data);
 
+/* ---- an entry point that allocates nothing ---------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Natural-order radix-2 FFT (inverse = 0) or inverse FFT incl. the 1/n factor (inverse != 0) of n = 2^log2n Fr elements
+ * -- the values zkb_domain_op(ZKB_NTT_FFT / ZKB_NTT_IFFT) gives on the basic radix-2 domain of size n, bit for bit.
+ * d_in, d_out: DEVICE pointers on the context's device, n x 4 limbs each (Montgomery Fr); they may be equal.
+ * All scratch (the working copy of the vector and the twiddle table) lives in one static device array inside
+ * libzkb.so: 768 KiB per GPU that loads the library, held until exit; hence log2n <= zkb_fft_noalloc_max_log2() = 14,
+ * larger sizes return ZKB_ERR_ARG (use zkb_domain_op).  The call performs no cudaMalloc / cudaFree and uses no
+ * allocating library routine; the first call on a device also looks up the array's address (cudaGetSymbolAddress).
+ * The array is shared by every call on that device and keeps the last call's contents (each call rewrites what it
+ * reads; nothing needs zeroing): calls that overlap on the GPU -- two contexts, two host threads -- race on it.  The
+ * call returns after its work on the context's stream has completed. */
+int zkb_fft_noalloc_max_log2(void);
+int zkb_fft_noalloc(zkb_ctx *ctx, int log2n, int inverse, const void *d_in, void *d_out);
+
 /* ---- the proving key ---------------------------------------------------------------- */
 /* CSR of one R1CS matrix: row i = constraint i; col 0 = the constant 1, col j > 0 = variable
  * j-1 of the full assignment (libsnark/relations/variable.tcc:262-270). */

@@ -53,6 +53,8 @@ SYMBOLS = {
     "zkb_msm_device": (_i, [_vp, _vp, _sz, _vp, _sz, _u64p]),
     "zkb_domain_select": (_i, [_sz, C.POINTER(_sz), C.POINTER(_i)]),
     "zkb_domain_op": (_i, [_vp, _sz, _i, _u64p]),
+    "zkb_fft_noalloc_max_log2": (_i, []),
+    "zkb_fft_noalloc": (_i, [_vp, _i, _i, _vp, _vp]),
     "zkb_key_upload": (_i, [_vp, _vp, C.POINTER(_vp)]),
     "zkb_key_free": (None, [_vp]),
     "zkb_key_device_bytes": (_sz, [_vp]),
@@ -332,6 +334,11 @@ class Context:
         d = np.array(_arr(data, 4), copy=True)
         self._chk(self.lib.zkb_domain_op(self.h, min_size, op, d.ctypes.data))
         return d
+
+    def fft_noalloc(self, log2n: int, inverse: bool, d_in: int, d_out: int) -> None:
+        """zkb_fft_noalloc: FFT / iFFT of 2^log2n Fr elements between DEVICE buffers (CUDA pointers, e.g. torch data_ptr()),
+        with all scratch in a static device array of libzkb.so: no allocation happens in the call"""
+        self._chk(self.lib.zkb_fft_noalloc(self.h, log2n, 1 if inverse else 0, C.c_void_p(d_in), C.c_void_p(d_out)))
 
     # ---- key / prover -----------------------------------------------------------------
     def upload_key(self, key: dict, rank: int = 0, world: int = 1) -> "Key":

@@ -22,6 +22,7 @@
 // the zklaim circuit).
 #include "ntt.cuh"
 #include "ntt_tile.cuh"
+#include <mutex>
 #include <stdlib.h>
 
 using namespace zkb;
@@ -657,6 +658,81 @@ int zkb_domain_op(zkb_ctx *ctx, size_t min_size, int op, uint64_t *data)
     }
     domain_free(&d);
     return rc;
+}
+
+} // extern "C"
+
+// ---- an entry point that allocates nothing (no counterpart in the reference) ----
+// Callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it) get
+// the natural-order radix-2 FFT / inverse FFT over Fr -- what r2_natural + the 1/n scaling do for zkb_domain_op on a
+// basic_radix2_domain -- with every byte of scratch in ONE file-scope device array: the working copy of the vector
+// (r2_natural's `tmp`, which zkb_domain_op takes from the context's grow-only cudaMalloc'ed scratch) and the twiddle
+// table w^i, i < n/2 (which zkb_domain_op cudaMallocs per call in r2_build).  Every GPU that loads libzkb.so holds the
+// array until exit: ZKB_FFT_NOALLOC_MAX_LOG2 = 14 -> 2^14 x 32 B (vector) + 2^13 x 32 B (twiddles) = 768 KiB.
+// The array is shared by every call on a device and keeps the last call's contents; nothing in it has to start at zero
+// (both regions are fully rewritten by each call before they are read), and calls that overlap on the GPU race on it.
+#define ZKB_FFT_NOALLOC_MAX_LOG2 14
+static __device__ __align__(256) unsigned char g_fft_noalloc_scratch[((size_t)32 << ZKB_FFT_NOALLOC_MAX_LOG2) + ((size_t)32 << (ZKB_FFT_NOALLOC_MAX_LOG2 - 1))];
+
+namespace {
+// In host code `g_fft_noalloc_scratch` is a host-side stand-in for the symbol, NOT a device address: the address is asked
+// for once per device, with that device current, and cached here.
+constexpr int NOALLOC_MAX_DEV = 64;
+void *g_noalloc_addr[NOALLOC_MAX_DEV] = {nullptr};
+std::mutex g_noalloc_mu;
+
+int noalloc_scratch(zkb_ctx *ctx, unsigned char **out)
+{
+    if (ctx->dev < 0 || ctx->dev >= NOALLOC_MAX_DEV) return fail(ctx, ZKB_ERR_ARG, "zkb_fft_noalloc: device ordinal out of range");
+    std::lock_guard<std::mutex> g(g_noalloc_mu);
+    if (!g_noalloc_addr[ctx->dev]) {
+        void *p = nullptr;
+        ZKB_CUDA(ctx, cudaGetSymbolAddress(&p, g_fft_noalloc_scratch)); // ctx->dev is current (set by the caller below)
+        if (!p) return fail(ctx, ZKB_ERR_CUDA, "zkb_fft_noalloc: cudaGetSymbolAddress returned NULL");
+        g_noalloc_addr[ctx->dev] = p;
+    }
+    *out = (unsigned char *)g_noalloc_addr[ctx->dev];
+    return ZKB_OK;
+}
+} // namespace
+
+extern "C" {
+
+int zkb_fft_noalloc_max_log2(void) { return ZKB_FFT_NOALLOC_MAX_LOG2; }
+
+int zkb_fft_noalloc(zkb_ctx *ctx, int log2n, int inverse, const void *d_in, void *d_out)
+{
+    if (!ctx || !d_in || !d_out) return fail(ctx, ZKB_ERR_ARG, "zkb_fft_noalloc: bad argument");
+    if (log2n < 1 || log2n > ZKB_FFT_NOALLOC_MAX_LOG2)
+        return fail(ctx, ZKB_ERR_ARG, "zkb_fft_noalloc: log2n must be 1 .. " + std::to_string(ZKB_FFT_NOALLOC_MAX_LOG2) +
+                                          " (the static scratch array holds 2^" + std::to_string(ZKB_FFT_NOALLOC_MAX_LOG2) +
+                                          " elements); larger transforms: zkb_domain_op");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    unsigned char *base = nullptr;
+    int rc = noalloc_scratch(ctx, &base);
+    if (rc) return rc;
+    const size_t n = (size_t)1 << log2n;
+    Fr *work = reinterpret_cast<Fr *>(base);                                                  // n elements
+    Fr *tw = reinterpret_cast<Fr *>(base + ((size_t)32 << ZKB_FFT_NOALLOC_MAX_LOG2));          // n / 2 elements
+    cudaStream_t st = ctx->stream;
+    // twiddles of this size and direction (rebuilt every call: the array may hold another call's table)
+    const Fr w = fr_root_of_unity(log2n);
+    if ((rc = powers(ctx, tw, n / 2, inverse ? w.inverse() : w, Fr::one()))) return rc;
+    ZKB_CUDA(ctx, cudaMemcpyAsync(work, d_in, n * sizeof(Fr), cudaMemcpyDeviceToDevice, st));
+    R2Tables T;
+    T.logn = log2n;
+    T.fwd = tw;
+    T.inv = tw;
+    // decimation in frequency in place (natural in, bit-reversed out), then the permutation straight into d_out
+    if ((rc = r2_levels(ctx, T, inverse != 0, false, work, n, 1, nullptr))) return rc;
+    k_bitrev<<<dim3(ceil_div(n, 128), 1), 128, 0, st>>>(work, reinterpret_cast<Fr *>(d_out), n, log2n);
+    ZKB_LAUNCH_CHECK(ctx);
+    if (inverse) { // iFFT = 1/n times the inverse transform (basic_radix2_domain.tcc:52-62)
+        const Fr ninv = fr_from_u64(n).inverse();
+        if ((rc = scale(ctx, reinterpret_cast<Fr *>(d_out), n, n, 1, nullptr, &ninv))) return rc;
+    }
+    ZKB_CUDA(ctx, cudaStreamSynchronize(st)); // the shared array is free again when the call returns
+    return ZKB_OK;
 }
 
 } // extern "C"
