@@ -289,7 +289,11 @@ int zkb_libsnark_prove_batch_ex(zklaim_ctx **ctxs, size_t n, int *results)
                 return -2;
         const CachedKey ck = key_for_ctx(ctxs[0]);
         const size_t nv = ck.num_variables;
-        std::vector<uint64_t> w(n * nv * 4), r(n * 4), s(n * 4);
+        /* 55 MB for 64 one-payload credentials: kept per caller thread (a fresh vector costs the zero-fill and the page
+         * faults on every batch); entries of credentials the host check rejects are zeroed below */
+        static thread_local std::vector<uint64_t> w;
+        if (w.size() < n * nv * 4) w.resize(n * nv * 4);
+        std::vector<uint64_t> r(n * 4), s(n * 4);
         std::vector<int> res(n, 0);
         int bad = 0;
 #pragma omp parallel for schedule(dynamic, 1)
@@ -297,6 +301,7 @@ int zkb_libsnark_prove_batch_ex(zklaim_ctx **ctxs, size_t n, int *results)
             std::vector<FrT> primary, auxiliary;
             if (!build_witness(ctxs[i], primary, auxiliary)) { /* only with ZKB_HOST_CHECK=1 */
                 res[i] = 1;
+                memset(&w[i * nv * 4], 0, nv * 32);
                 continue;
             }
             if (primary.size() + auxiliary.size() != nv) {

@@ -404,6 +404,11 @@ template <class PR> struct Fp {
         r.reduce_once();
         return r;
     }
+    // Squaring = the general product.  A dedicated square (28 cross products formed once and doubled + 8 diagonal ones:
+    // 36 + 72 = 108 wide multiply-adds instead of 136, bit-exact on every GPU test) was built and measured in round 2 and
+    // REJECTED: the bucket accumulation, whose mixed addition holds 2 squares in 10 products, went from 6.17 ms to 6.29 ms
+    // per launch (one column walk) and 6.37 ms (two interleaved walks) -- the ~130 extra add / shift / move instructions
+    // and the longer dependent chain cost more than the 4 % of multiplier-pipe work saved; batch verification: unchanged.
     ZKB_HD Fp sqr() const { return (*this) * (*this); }
 
     // out of / into Montgomery form (fp.tcc:228-238 as_bigint; :190-196 constructor)

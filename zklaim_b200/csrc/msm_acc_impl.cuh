@@ -16,7 +16,7 @@ k_accumulate(const Affine<F> *__restrict__ pts, const uint32_t *__restrict__ ent
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t E = start[B];
-    const uint32_t S = msm_run_length(E, rmax);
+    const uint32_t S = msm_run_length<F>(E, rmax);
     const uint64_t lo64 = (uint64_t)t * S;
     if (lo64 >= E) return;
     const uint32_t lo = (uint32_t)lo64;

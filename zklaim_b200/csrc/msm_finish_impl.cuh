@@ -33,7 +33,7 @@ k_fixup(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, XYZZ<F> *
         const XYZZ<F> *__restrict__ parts, uint32_t *__restrict__ wide_list, uint32_t max_chunks)
 {
     extern __shared__ uint32_t sm[];
-    const uint32_t S = msm_run_length(start[B], rmax);
+    const uint32_t S = msm_run_length<F>(start[B], rmax);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t *wsm = sm + (size_t)wid * 32 * (sizeof(XYZZ<F>) / 4);
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -112,7 +112,7 @@ k_fixup_wide(const uint32_t *__restrict__ start, uint32_t B, uint32_t rmax, cons
              const uint32_t *__restrict__ wide_list, XYZZ<F> *__restrict__ chunk_sums)
 {
     extern __shared__ uint32_t sm[];
-    const uint32_t S = msm_run_length(start[B], rmax);
+    const uint32_t S = msm_run_length<F>(start[B], rmax);
     const int T = blockDim.x, t = threadIdx.x;
     const uint32_t count = wide_list[0];
     const uint32_t *chunks = wide_list + 2;

@@ -72,10 +72,10 @@ int msm_run(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, const uint32_t
 // most `rmax` runs of S = 32, 64, 128, ... pairs; every kernel derives S from E the same way.  (S started at 4 in
 // round 1: with few pairs most of the additions then moved into the fix-up pass, which merges run-boundary partials
 // with FULL additions -- 0.48 of the 2.1 ms of a single zklaim proof.)
-constexpr uint32_t MSM_MIN_RUN = 32;
-__host__ __device__ inline uint32_t msm_run_length(uint32_t E, uint32_t rmax)
+// G2 (Fq2 coordinates: three times the work per addition, a third of the resident threads) keeps shorter runs.
+template <class F> __host__ __device__ inline uint32_t msm_run_length(uint32_t E, uint32_t rmax)
 {
-    uint32_t S = MSM_MIN_RUN;
+    uint32_t S = sizeof(F) > 32 ? 8u : 32u;
     while ((uint64_t)S * rmax < E) S <<= 1;
     return S;
 }

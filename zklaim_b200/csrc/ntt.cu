@@ -24,6 +24,7 @@
 #include "ntt_tile.cuh"
 #include <mutex>
 #include <stdlib.h>
+#include <string.h>
 
 using namespace zkb;
 
@@ -162,6 +163,33 @@ k_ntt_r8(Fr *__restrict__ data, size_t vstride, const NttPass P, const Fr *__res
         __syncthreads();
     }
     ntt_tile_store(P, tid, T, sm, a, blockIdx.x, post);
+}
+
+// the same pass with the fused steps of the witness map's last transform (NttFuse): a separate kernel, so that the plain
+// passes carry neither the extra parameters nor the extra code
+template <bool DIT>
+__global__ void __launch_bounds__(256, 2)
+k_ntt_r8_h(Fr *__restrict__ data, size_t vstride, const NttPass P, const Fr *__restrict__ tw, NttFuse f, size_t hstride)
+{
+    extern __shared__ uint32_t sm[];
+    const size_t voff = (size_t)blockIdx.y * vstride;
+    Fr *a = data + voff;
+    if (f.B) { // B and C live at fixed distances from the A vector (the caller passes them for vector 0)
+        f.B += voff;
+        f.C += voff;
+    }
+    if (f.h_mont) {
+        f.h_mont += (size_t)blockIdx.y * hstride;
+        if (f.h_plain) f.h_plain += (size_t)blockIdx.y * hstride;
+    }
+    const int tid = threadIdx.x, T = blockDim.x;
+    ntt_tile_load(P, tid, T, sm, a, blockIdx.x, &f);
+    __syncthreads();
+    for (int rd = 0; rd < P.nrounds; rd++) {
+        ntt_tile_round_any<DIT>(P, rd, tid, sm, blockIdx.x, tw);
+        __syncthreads();
+    }
+    ntt_tile_store(P, tid, T, sm, a, blockIdx.x, nullptr, &f);
 }
 
 // out[bitrev(i)] = in[i]
@@ -357,7 +385,10 @@ int r2_build(zkb_ctx *ctx, R2Tables *t, int logn, size_t *bytes)
 
 // all butterfly levels of size 2^T.logn on nvec vectors, in place.
 // dit = false: natural in, bit-reversed out; dit = true: bit-reversed in, natural out.
-int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, size_t vstride, int nvec, const Fr *post)
+// fuse (optional): the H transform of the witness map -- the first pass computes (A B - C) zinv while loading, the
+// last pass writes h = value * cos_inv in natural order to fuse->h_mont / h_plain (see NttFuse); needs r8 passes throughout
+int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, size_t vstride, int nvec, const Fr *post,
+              const NttFuse *fuse = nullptr, size_t hstride = 0)
 {
     const int L = T.logn;
     if (L == 0) return ZKB_OK;
@@ -366,6 +397,10 @@ int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, si
         ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_pass<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
         ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
         ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8_h<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8_h<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, NTT_EMAX * 32));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8_h<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8_h<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         ctx->func_attr_done |= 1u;
@@ -377,6 +412,9 @@ int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, si
     }();
     NttPlan pl;
     ntt_plan_transform(&pl, L, dit, tile_log);
+    if (fuse)
+        for (int p = 0; p < pl.npass; p++)
+            if (!pl.r8[p]) return fail(ctx, ZKB_ERR_ARG, "r2_levels: fused H transform needs a domain of at least 256 points");
     const Fr *tw = inverse ? T.inv : T.fwd;
     for (int p = 0; p < pl.npass; p++) {
         const NttPass &P = pl.pass[p];
@@ -385,7 +423,25 @@ int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, si
         const Fr *pp = p == pl.npass - 1 ? post : nullptr;
         if (pl.r8[p]) {
             const unsigned threads = 1u << (P.k + P.logC - 3);
-            if (dit)
+            const bool first = p == 0, last = p == pl.npass - 1;
+            if (fuse && (first || last)) {
+                NttFuse f;
+                memset(&f, 0, sizeof(f));
+                if (first) {
+                    f.B = fuse->B;
+                    f.C = fuse->C;
+                    f.zinv = fuse->zinv;
+                }
+                if (last) {
+                    f.h_mont = fuse->h_mont;
+                    f.h_plain = fuse->h_plain;
+                    f.cos_inv = fuse->cos_inv;
+                }
+                if (dit)
+                    k_ntt_r8_h<true><<<dim3(blocks, nvec), threads, smem, ctx->stream>>>(a, vstride, P, tw, f, hstride);
+                else
+                    k_ntt_r8_h<false><<<dim3(blocks, nvec), threads, smem, ctx->stream>>>(a, vstride, P, tw, f, hstride);
+            } else if (dit)
                 k_ntt_r8<true><<<dim3(blocks, nvec), threads, smem, ctx->stream>>>(a, vstride, P, tw, pp);
             else
                 k_ntt_r8<false><<<dim3(blocks, nvec), threads, smem, ctx->stream>>>(a, vstride, P, tw, pp);
@@ -599,6 +655,24 @@ int domain_to_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nv
     int rc = step_ifft(ctx, d, a, vstride, nvec, tmp, nullptr, vstride, d->cos_fwd);
     if (!rc) rc = step_fft(ctx, d, tmp, a, vstride, nvec, nullptr);
     return rc;
+}
+
+// (A B - C) / Z on the coset and the inverse coset transform in one go, for the basic domain: the pointwise step rides on
+// the loads of the first pass, the g^-i / m scaling, the un-permutation and the plain-integer copy on the stores of the last
+// pass (r1cs_to_qap.tcc:270-311).  abc = [A (nvec vectors) | B | C], vector v of matrix k at abc + (k * nvec + v) * m.
+// Returns ZKB_ERR_DOMAIN when the domain does not qualify (step domain, fewer than 256 points): callers use the two-step form.
+int domain_h_fused(zkb_ctx *ctx, const Domain *d, Fr *abc, int nvec, Fr *h_mont, Fr *h_plain, size_t hstride)
+{
+    if (d->kind != ZKB_DOMAIN_BASIC_RADIX2 || d->big.logn < 8) return ZKB_ERR_DOMAIN;
+    NttFuse f;
+    memset(&f, 0, sizeof(f));
+    f.B = abc + (size_t)nvec * d->m;
+    f.C = abc + (size_t)2 * nvec * d->m;
+    f.zinv = d->zinv;
+    f.h_mont = h_mont;
+    f.h_plain = h_plain;
+    f.cos_inv = d->cos_inv;
+    return r2_levels(ctx, d->big, true, false, abc, d->m, nvec, nullptr, &f, hstride);
 }
 
 int domain_h_from_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp, Fr *h_mont, Fr *h_plain,

@@ -49,6 +49,9 @@ int domain_to_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nv
 // h_plain != NULL, their plain-integer form to h_plain + v * hstride.
 int domain_h_from_coset(zkb_ctx *ctx, const Domain *d, Fr *a, size_t vstride, int nvec, Fr *tmp, Fr *h_mont,
                         Fr *h_plain, size_t hstride);
+// the same with the pointwise step (A B - C) / Z folded in (basic domain of >= 256 points; else ZKB_ERR_DOMAIN and nothing
+// is enqueued): abc = [A | B | C], nvec vectors each, on the coset; A is destroyed
+int domain_h_fused(zkb_ctx *ctx, const Domain *d, Fr *abc, int nvec, Fr *h_mont, Fr *h_plain, size_t hstride);
 // single natural-order operation (ZKB_NTT_*), in place
 int domain_op(zkb_ctx *ctx, const Domain *d, int op, Fr *a, size_t vstride, int nvec, Fr *tmp);
 

@@ -110,19 +110,34 @@ ZKB_HD size_t ntt_gidx(const NttPass &P, uint32_t blk, int t, int col)
 }
 
 // ---- load / store phases: lanes walk consecutive global addresses ------------------------------------------
+// (Measured and rejected in round 2: letting the first round load and the last round store straight from / to global
+//  memory, without the staging here -- the lanes of a round then touch 32 different 128-byte lines per instruction:
+//  witness map at 2^22 8.13 -> 8.38 ms.)
+// Optional fused steps of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:270-311), used by its last transform only:
+struct NttFuse {
+    const Fr *B, *C; // load: the staged value becomes (a * B[i] - C[i]) * zinv   (H on the coset, divided by Z)
+    Fr zinv;
+    Fr *h_mont, *h_plain; // store: instead of the in-place store, h[bitrev_L(i)] = value * cos_inv[bitrev_L(i)], natural
+    const Fr *cos_inv;    // order, Montgomery form to h_mont and (optional) plain integers to h_plain
+};
+
 // lobits < logC: the 2^logC columns of a tile do not form one contiguous run, the t index does (tfast)
-ZKB_HD void ntt_tile_load(const NttPass &P, int tid, int T, uint32_t *sm, const Fr *a, uint32_t blk)
+ZKB_HD void ntt_tile_load(const NttPass &P, int tid, int T, uint32_t *sm, const Fr *a, uint32_t blk, const NttFuse *f = nullptr)
 {
     const int E = 1 << (P.k + P.logC), C = 1 << P.logC;
     const bool tfast = P.lobits < P.logC;
     for (int e = tid; e < E; e += T) {
         const int col = tfast ? (e >> P.k) : (e & (C - 1));
         const int t = tfast ? (e & ((1 << P.k) - 1)) : (e >> P.logC);
-        ntt_sm_put(sm, E, (t << P.logC) + col, ntt_ld(a + ntt_gidx(P, blk, t, col)));
+        const size_t g = ntt_gidx(P, blk, t, col);
+        Fr v = ntt_ld(a + g);
+        if (f && f->B) v = Fr::mont_mul_inline(Fr::mont_mul_inline(v, ntt_ld(f->B + g)) - ntt_ld(f->C + g), f->zinv);
+        ntt_sm_put(sm, E, (t << P.logC) + col, v);
     }
 }
 // post (optional): result multiplied by post[bitrev_L(index)] on the way out
-ZKB_HD void ntt_tile_store(const NttPass &P, int tid, int T, const uint32_t *sm, Fr *a, uint32_t blk, const Fr *post)
+ZKB_HD void ntt_tile_store(const NttPass &P, int tid, int T, const uint32_t *sm, Fr *a, uint32_t blk, const Fr *post,
+                           const NttFuse *f = nullptr)
 {
     const int E = 1 << (P.k + P.logC), C = 1 << P.logC;
     const bool tfast = P.lobits < P.logC;
@@ -131,6 +146,13 @@ ZKB_HD void ntt_tile_store(const NttPass &P, int tid, int T, const uint32_t *sm,
         const int t = tfast ? (e & ((1 << P.k) - 1)) : (e >> P.logC);
         const size_t g = ntt_gidx(P, blk, t, col);
         Fr v = ntt_sm_get(sm, E, (t << P.logC) + col);
+        if (f && f->h_mont) {
+            const uint32_t i = ntt_brev((uint32_t)g, P.L);
+            v = Fr::mont_mul_inline(v, ntt_ld_ro(f->cos_inv + i));
+            ntt_st(f->h_mont + i, v);
+            if (f->h_plain) ntt_st(f->h_plain + i, v.from_mont());
+            continue;
+        }
         if (post) v = Fr::mont_mul_inline(v, ntt_ld_ro(post + ntt_brev((uint32_t)g, P.L)));
         ntt_st(a + g, v);
     }

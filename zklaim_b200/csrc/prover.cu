@@ -288,7 +288,8 @@ __device__ __forceinline__ void run(const uint32_t (*prog)[4], int nsteps, uint3
         const Fq x = Rg[a], y = Rg[b];
         Fq t;
         if ((mul_steps >> s) & 1u) {
-            t = x * y;
+            t = Fq::mont_mul_inline(x, y); // the one product of this machine: expanded in place (the out-of-line multiplier of
+                                           // this translation unit passes its operands through local memory)
         } else {
             const Fq sum = x + y, dif = x - y;
             t = op == ADD ? sum : op == SUB ? dif : op == SUB2 ? dif - y : sum + x;
@@ -741,6 +742,8 @@ int witness_map_chunk(zkb_ctx *ctx, const zkb_key *key, int batch, uint32_t *d_f
     }
     rc = domain_to_coset(ctx, &key->dom, abc, m, 3 * batch, tmp);
     if (rc) return rc;
+    rc = domain_h_fused(ctx, &key->dom, abc, batch, Z + key->z_h(), P + key->z_h(), key->zlen);
+    if (rc != ZKB_ERR_DOMAIN) return rc;
     const bool basic = key->kind == ZKB_DOMAIN_BASIC_RADIX2;
     k_h_pointwise<<<dim3(ceil_div(m, 128), batch), 128, 0, st>>>(abc, m, batch, key->dom.zinv, basic ? nullptr : key->dom.zinv_tab);
     ZKB_LAUNCH_CHECK(ctx);
