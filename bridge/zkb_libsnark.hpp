@@ -426,7 +426,10 @@ class Session {
         if (pool_) zkb_pool_shutdown(pool_);
         pool_ = NULL;
     }
-    ~Session() { clear(); }
+    /* no CUDA call from a static destructor: at process exit the CUDA runtime may already be torn down (with several
+     * devices in use that ends in a fault inside the driver).  Callers that want the memory back call zkb_bridge_reset();
+     * otherwise the process exit releases it. */
+    ~Session() {}
 
   private:
     zkb_pool *pool_locked()

@@ -293,6 +293,7 @@ int zkb_libsnark_prove_batch_ex(zklaim_ctx **ctxs, size_t n, int *results)
          * faults on every batch); entries of credentials the host check rejects are zeroed below */
         static thread_local std::vector<uint64_t> w;
         if (w.size() < n * nv * 4) w.resize(n * nv * 4);
+        uint64_t *const wp = w.data(); /* the OpenMP workers below must not name `w`: each has its own (empty) thread_local */
         std::vector<uint64_t> r(n * 4), s(n * 4);
         std::vector<int> res(n, 0);
         int bad = 0;
@@ -301,7 +302,7 @@ int zkb_libsnark_prove_batch_ex(zklaim_ctx **ctxs, size_t n, int *results)
             std::vector<FrT> primary, auxiliary;
             if (!build_witness(ctxs[i], primary, auxiliary)) { /* only with ZKB_HOST_CHECK=1 */
                 res[i] = 1;
-                memset(&w[i * nv * 4], 0, nv * 32);
+                memset(wp + i * nv * 4, 0, nv * 32);
                 continue;
             }
             if (primary.size() + auxiliary.size() != nv) {
@@ -309,7 +310,7 @@ int zkb_libsnark_prove_batch_ex(zklaim_ctx **ctxs, size_t n, int *results)
                 bad = 2;
                 continue;
             }
-            pack_assignment(primary, auxiliary, &w[i * nv * 4]);
+            pack_assignment(primary, auxiliary, wp + i * nv * 4);
         }
         if (bad) return -2;
         /* credentials the host check rejected keep a zero assignment: the device reports them unsatisfied as well */
@@ -325,9 +326,9 @@ int zkb_libsnark_prove_batch_ex(zklaim_ctx **ctxs, size_t n, int *results)
             std::lock_guard<std::mutex> gpu(Session::get().gpu());
             size_t first_ok = 0;
             while (first_ok < n && res[first_ok]) first_ok++;
-            if (first_ok < n) Session::get().tune_once(ck.keys, &w[first_ok * nv * 4]);
+            if (first_ok < n) Session::get().tune_once(ck.keys, wp + first_ok * nv * 4);
             zkb_pool *pool = Session::get().pool();
-            rc = zkb_pool_prove_batch(pool, ck.keys, n, w.data(), r.data(), s.data(), out.data(), status.data());
+            rc = zkb_pool_prove_batch(pool, ck.keys, n, wp, r.data(), s.data(), out.data(), status.data());
             if (rc != ZKB_OK) err = zkb_pool_last_error(pool);
         }
         if (rc != ZKB_OK && rc != ZKB_ERR_UNSAT) {
