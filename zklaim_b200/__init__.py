@@ -405,9 +405,15 @@ class Context:
         return out
 
     def prove_split_begin(self, key: "Key", w, r, s, which: int, check: bool, d_part: int = 0) -> None:
-        """zkb_prove_split_begin: d_part = CUDA device pointer (m x 4 limbs) when which in (0, 1, 2)"""
-        w, r, s = _arr(w, 4), _arr(r, 4), _arr(s, 4)
-        self._chk(self.lib.zkb_prove_split_begin(self.h, key.h, w.ctypes.data, r.ctypes.data, s.ctypes.data, which, 1 if check else 0,
+        """zkb_prove_split_begin: d_part = CUDA device pointer (m x 4 limbs) when which in (0, 1, 2); w = host array, or an
+        int = CUDA device pointer to the num_variables x 4 limbs on this context's GPU"""
+        r, s = _arr(r, 4), _arr(s, 4)
+        if isinstance(w, int):
+            wp = C.c_void_p(w)
+        else:
+            w = _arr(w, 4)
+            wp = C.c_void_p(w.ctypes.data)
+        self._chk(self.lib.zkb_prove_split_begin(self.h, key.h, wp, r.ctypes.data, s.ctypes.data, which, 1 if check else 0,
                                                  C.c_void_p(d_part)))
 
     def prove_split_combine(self, key: "Key", d_abc: int, d_H: int) -> None:

@@ -28,6 +28,7 @@
 #define ZKB_NOINLINE_MUL 1
 #include "msm_impl.cuh"
 #include "ntt.cuh"
+#include "glv.cuh"
 #include <string.h>
 #include <algorithm>
 
@@ -231,7 +232,8 @@ __global__ void k_z_plain(const Fr *__restrict__ Z, Fr *__restrict__ P, size_t z
 }
 
 // ---- the two variable-base scalar multiplications of r1cs_gg_ppzksnark.tcc:495 ------------------------------
-// sm[2p] = s * g1_A, sm[2p + 1] = r * g1_B.  The chain of 252 doublings is serial and a warp instruction costs the
+// sm[2p] = s * g1_A, sm[2p + 1] = r * g1_B.  The scalar is split with the curve's endomorphism (glv.cuh: k B =
+// k1 B + |k2| (-phi(B)), halves below 2^128), which leaves a chain of 128 doublings; that chain is serial and a warp instruction costs the
 // same for one active lane as for 32, so the parallelism available is INSIDE a point operation: the independent
 // field products of an XYZZ doubling (9 products, depth 3) and addition (14 products, depth 4) are spread over four
 // lanes that run one uniform instruction stream -- a tiny register machine whose registers live in shared memory.
@@ -304,11 +306,14 @@ __device__ __forceinline__ void run(const uint32_t (*prog)[4], int nsteps, uint3
 __global__ void __launch_bounds__(64)
 k_smul(const G1X *__restrict__ rab, const Fr *__restrict__ Pl, size_t zlen, size_t off_r, size_t off_s, G1X *__restrict__ sm)
 {
-    __shared__ Fq regs[2][96];
+    // registers 0 .. 31: the machine's; 32 + 4 d: T[d] = d B; 96 + 4 d: U[d] = -phi(T[d]) = (beta x, -y) (glv.cuh)
+    __shared__ Fq regs[2][160];
+    __shared__ uint32_t halves[2][2][5];
     const int p = blockIdx.x, which = threadIdx.x >> 5, lane = threadIdx.x & 31; // 0: s * g1_A, 1: r * g1_B
     if (lane >= 4) return;
     Fq *Rg = regs[which];
     const Fr k = ld_vec(Pl + (size_t)p * zlen + (which == 0 ? off_s : off_r)); // plain integers
+    if (lane == 0) glv::decompose(k.v, halves[which][0], halves[which][1]);   // k = k1 - |k2| lambda, both below 2^128
     const G1X *src = rab + 2 * (size_t)p + which;
     G1X *dst = sm + 2 * (size_t)p + which;
     const Fq *srcw = reinterpret_cast<const Fq *>(src);
@@ -334,20 +339,38 @@ k_smul(const G1X *__restrict__ rab, const Fr *__restrict__ Pl, size_t zlen, size
             }
             copy(32 + 4 * d, vm::X);
         }
+        {
+            Fq beta;
+            const uint32_t bm[8] = ZKB_GLV_BETA_MONT;
+#pragma unroll
+            for (int i = 0; i < 8; i++) beta.v[i] = bm[i];
+            for (int e = 1 + lane; e < 16; e += 4) { // U[e]: one product per entry, entries dealt over the four lanes
+                Rg[96 + 4 * e + vm::X] = Fq::mont_mul_inline(Rg[32 + 4 * e + vm::X], beta);
+                Rg[96 + 4 * e + vm::Y] = Rg[32 + 4 * e + vm::Y].neg();
+                Rg[96 + 4 * e + vm::ZZ] = Rg[32 + 4 * e + vm::ZZ];
+                Rg[96 + 4 * e + vm::ZZZ] = Rg[32 + 4 * e + vm::ZZZ];
+            }
+            __syncwarp(0xfu);
+        }
+        const uint32_t *k1 = halves[which][0], *k2 = halves[which][1];
         bool acc_inf = true;
-        for (int w = 63; w >= 0; w--) {
+        auto add_entry = [&](int entry) {
+            if (acc_inf) {
+                copy(vm::X, entry);
+                acc_inf = false;
+                return;
+            }
+            vm::run(vm::ADDA, 2, vm::ADDA_MUL_STEPS, Rg, entry, lane);
+            fallback |= Rg[vm::P].is_zero(); // the accumulator never equals +- a table entry for halves below 2^128 (the lattice of
+                                             // glv.cuh has no vector that short); guarded all the same
+            vm::run(vm::ADDB, 7, vm::ADDB_MUL_STEPS, Rg, entry, lane);
+        };
+        for (int w = 32; w >= 0; w--) { // 33 windows of 4 bits: one past the 128 bits of the halves
             if (!acc_inf)
                 for (int i = 0; i < 4; i++) vm::run(vm::DBL, 8, vm::DBL_MUL_STEPS, Rg, 0, lane);
-            const int d = (int)((k.v[w >> 3] >> ((w & 7) * 4)) & 15u);
-            if (!d) continue;
-            if (acc_inf) {
-                copy(vm::X, 32 + 4 * d);
-                acc_inf = false;
-                continue;
-            }
-            vm::run(vm::ADDA, 2, vm::ADDA_MUL_STEPS, Rg, 32 + 4 * d, lane);
-            fallback |= Rg[vm::P].is_zero(); // 16 m P == +- d P cannot happen for m < r / 16; guarded all the same
-            vm::run(vm::ADDB, 7, vm::ADDB_MUL_STEPS, Rg, 32 + 4 * d, lane);
+            const int d1 = (int)((k1[w >> 3] >> ((w & 7) * 4)) & 15u), d2 = (int)((k2[w >> 3] >> ((w & 7) * 4)) & 15u);
+            if (d1) add_entry(32 + 4 * d1);
+            if (d2) add_entry(96 + 4 * d2);
         }
         if (acc_inf) { // k == 0
             Rg[lane] = Fq::zero();
@@ -1068,7 +1091,8 @@ int zkb_prove_split_begin(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, c
     Fr *Z = ctx->scratch[SP_Z].as<Fr>();
     Fr *rs = ctx->scratch[SP_RS].as<Fr>();
     uint32_t *flags = ctx->scratch[SP_FLAGS].as<uint32_t>();
-    if (nv) ZKB_CUDA(ctx, cudaMemcpyAsync(Z + 1, w, nv * sizeof(Fr), cudaMemcpyHostToDevice, st));
+    // w: host memory, or device memory of this GPU (a witness gathered over NVLink, sharding.sharded_prove_split)
+    if (nv) ZKB_CUDA(ctx, cudaMemcpyAsync(Z + 1, w, nv * sizeof(Fr), cudaMemcpyDefault, st));
     ZKB_CUDA(ctx, cudaMemcpyAsync(rs, r, sizeof(Fr), cudaMemcpyHostToDevice, st));
     ZKB_CUDA(ctx, cudaMemcpyAsync(rs + 1, s, sizeof(Fr), cudaMemcpyHostToDevice, st));
     ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, st));

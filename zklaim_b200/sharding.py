@@ -81,13 +81,19 @@ def sharded_prove(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndarray, g
     return ctx.prove_combine(parts, r, s)
 
 
-def sharded_prove_split(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndarray, group=None, device: Optional[str] = None) -> np.ndarray:
+def sharded_prove_split(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndarray, group=None, device: Optional[str] = None,
+                        trace: Optional[dict] = None) -> np.ndarray:
     """ONE Groth16 proof over all ranks with the witness map SPLIT by polynomial instead of replicated (needs >= 3 ranks;
     fewer fall back to sharded_prove).  r1cs_to_qap_witness_map treats A, B and C alike (r1cs_to_qap.tcc:240-293): ranks
     0 / 1 / 2 run SpMV + iFFT + coset FFT of one polynomial each (zkb_prove_split_begin), ranks 1 and 2 send their m x 32
     bytes to rank 0 (NCCL send / recv), rank 0 divides by Z and transforms back (zkb_prove_split_combine), broadcasts the H
     coefficients, and every rank computes its share of the H + L sum (zkb_prove_split_end); the witness-only sums run on
-    side streams from the start.  The last rank also checks satisfiability.  Exchanges: 2 x 32 m bytes in, 32 m bytes out."""
+    side streams from the start.  The last rank also checks satisfiability.  Exchanges: 2 x 32 m bytes in, 32 m bytes out.
+    On GPUs the witness itself travels the same way: every rank copies ONE range of it over PCIe and an all_gather over
+    NVLink completes it on every GPU (the full copy per rank costs 124 MB / PCIe rate for the 2^22 circuit).
+    `trace` (optional dict) receives this rank's wall time per phase in ms (the syncs between phases are there anyway)."""
+    import time
+
     import torch
     import torch.distributed as dist
 
@@ -105,17 +111,47 @@ def sharded_prove_split(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndar
     abc = torch.empty((3, m, 4), dtype=torch.int64, device=dev) if rank == 0 else None
     part = abc[0] if rank == 0 else (torch.empty((m, 4), dtype=torch.int64, device=dev) if which >= 0 else None)
     H = torch.empty((m, 4), dtype=torch.int64, device=dev)
+    t_last = [time.perf_counter()]
+
+    def mark(name):
+        if trace is not None:
+            now = time.perf_counter()
+            trace[name] = trace.get(name, 0.0) + 1e3 * (now - t_last[0])
+            t_last[0] = now
+
+    w_arg = w
+    if dev.type == "cuda":
+        w2 = np.ascontiguousarray(w, dtype=np.uint64).reshape(-1, 4)
+        nv = w2.shape[0]
+        per = -(-nv // world)
+        W = torch.empty((per * world, 4), dtype=torch.int64, device=dev)
+        lo, hi = min(rank * per, nv), min((rank + 1) * per, nv)
+        mine = W[rank * per:(rank + 1) * per]
+        if hi > lo:
+            mine[:hi - lo].copy_(torch.from_numpy(w2[lo:hi].view(np.int64)), non_blocking=True)
+        dist.all_gather_into_tensor(W, mine, group=group)
+        w_arg = W.data_ptr()
     sync()
-    ctx.prove_split_begin(key_shard, w, r, s, which, check=(rank == world - 1), d_part=part.data_ptr() if part is not None else 0)
+    mark("witness: one range per rank over PCIe, all_gather over NVLink")
+    ctx.prove_split_begin(key_shard, w_arg, r, s, which, check=(rank == world - 1), d_part=part.data_ptr() if part is not None else 0)
+    mark("begin: own polynomial to the coset (ranks 0-2)")
     if rank == 0:
-        dist.recv(abc[1], src=1, group=group)
-        dist.recv(abc[2], src=2, group=group)
+        for q in dist.batch_isend_irecv([dist.P2POp(dist.irecv, abc[1], 1, group), dist.P2POp(dist.irecv, abc[2], 2, group)]):
+            q.wait()
         sync()
+        mark("recv 2 x 32 m bytes")
         ctx.prove_split_combine(key_shard, abc.data_ptr(), H.data_ptr())
+        mark("combine: (A B - C) / Z, coset back to coefficients")
     elif rank in (1, 2):
-        dist.send(part, dst=0, group=group)
+        for q in dist.batch_isend_irecv([dist.P2POp(dist.isend, part, 0, group)]):
+            q.wait()
     dist.broadcast(H, src=0, group=group)
     sync()
+    mark("broadcast of H (32 m bytes)")
     share = ctx.prove_split_end(key_shard, H.data_ptr())
+    mark("end: H + L sums over this rank's ranges, witness-only sums joined")
     parts = gather_partials(share, group, device)
-    return ctx.prove_combine(parts, r, s)
+    mark("all_gather of the 480-byte shares")
+    out = ctx.prove_combine(parts, r, s)
+    mark("assembly")
+    return out
