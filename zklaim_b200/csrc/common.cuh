@@ -66,6 +66,8 @@ struct zkb_ctx {
     zkb::DevBuf scratch[64];
     void *pinned = nullptr; // small pinned staging area for results
     size_t pinned_cap = 0;
+    void *stage = nullptr; // pinned staging area for large inputs that arrive in pageable memory (upload_rows)
+    size_t stage_cap = 0;
     // optional profiling of the dominant kernel (bucket accumulation), per group: [0] = G1, [1] = G2
     bool prof = false;
     cudaEvent_t pe[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
@@ -170,6 +172,9 @@ inline unsigned ceil_div(size_t a, size_t b) { return (unsigned)((a + b - 1) / b
 
 // host-side helpers implemented in api.cu
 int ensure_pinned(zkb_ctx *ctx, size_t bytes);
+// `rows` rows of `width` bytes from host (pageable or pinned) or device memory at src (pitch spitch) to device rows at
+// dst (pitch dpitch), ordered on `st`.  Large pageable inputs go through ctx->stage with several host threads copying.
+int upload_rows(zkb_ctx *ctx, void *dst, size_t dpitch, const void *src, size_t spitch, size_t width, size_t rows, cudaStream_t st);
 // folds the event pairs recorded since the last call into the profile counters (stream must be idle)
 void prof_collect(zkb_ctx *ctx);
 

@@ -872,8 +872,10 @@ int prove_impl(zkb_ctx *ctx, const zkb_key *key, size_t count, const uint64_t *w
         Fr *rs = ctx->scratch[SP_RS].as<Fr>();
         uint32_t *flags = ctx->scratch[SP_FLAGS].as<uint32_t>();
         zkb_proof *d_out = ctx->scratch[SP_PROOF].as<zkb_proof>();
-        if (nv)
+        if (nv && dev_in)
             ZKB_CUDA(ctx, cudaMemcpy2DAsync(Z + 1, zlen * sizeof(Fr), w + base * nv * 4, nv * sizeof(Fr), nv * sizeof(Fr), batch, kin, st));
+        if (nv && !dev_in && upload_rows(ctx, Z + 1, zlen * sizeof(Fr), w + base * nv * 4, nv * sizeof(Fr), nv * sizeof(Fr), batch, st))
+            return ZKB_ERR_CUDA;
         if (map_only) {
             ZKB_CUDA(ctx, cudaMemsetAsync(rs, 0, (size_t)batch * 2 * sizeof(Fr), st));
         } else {
@@ -1092,7 +1094,7 @@ int zkb_prove_split_begin(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, c
     Fr *rs = ctx->scratch[SP_RS].as<Fr>();
     uint32_t *flags = ctx->scratch[SP_FLAGS].as<uint32_t>();
     // w: host memory, or device memory of this GPU (a witness gathered over NVLink, sharding.sharded_prove_split)
-    if (nv) ZKB_CUDA(ctx, cudaMemcpyAsync(Z + 1, w, nv * sizeof(Fr), cudaMemcpyDefault, st));
+    if (nv && upload_rows(ctx, Z + 1, nv * sizeof(Fr), w, nv * sizeof(Fr), nv * sizeof(Fr), 1, st)) return ZKB_ERR_CUDA;
     ZKB_CUDA(ctx, cudaMemcpyAsync(rs, r, sizeof(Fr), cudaMemcpyHostToDevice, st));
     ZKB_CUDA(ctx, cudaMemcpyAsync(rs + 1, s, sizeof(Fr), cudaMemcpyHostToDevice, st));
     ZKB_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
