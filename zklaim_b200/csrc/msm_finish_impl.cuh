@@ -2,6 +2,7 @@
 // base precomputation (see msm.cu for the design).  Latency-bound: built with ZKB_NOINLINE_MUL.
 #pragma once
 #include "msm_impl.cuh"
+#include <algorithm>
 
 namespace zkb {
 // word-striped shared-memory staging (conflict-free for any struct size)
@@ -265,6 +266,90 @@ k_reduce_l2(const XYZZ<F> *__restrict__ l1, int NB, int logCH, XYZZ<F> *__restri
     }
 }
 
+// ---- the two levels above for ALL jobs of a plan in one launch each -------------------------------------------------
+// A single proof leaves the device nearly empty and the reduction of a job is a chain of ~45 dependent point
+// additions (0.23 ms in G1): the jobs of a plan (A and B1 queries) are independent, so their chains run side by side
+// instead of one after the other.  blockIdx.z = job; blocks outside a job's geometry leave at once.
+struct RedGeo {
+    uint32_t bucket_off, G, nb, sets;
+    int T, L, logL, NB, logCH, c;
+    uint32_t l1_off, l2_off; // first (R, S) pair / first set result of this job
+};
+struct RedGeoTab {
+    RedGeo g[MSM_MAX_JOBS];
+};
+template <class F>
+__global__ void __launch_bounds__(128)
+k_reduce_l1_jobs(const XYZZ<F> *__restrict__ buckets, uint32_t Bp, RedGeoTab tab, XYZZ<F> *__restrict__ out)
+{
+    extern __shared__ uint32_t sm[];
+    const RedGeo &J = tab.g[blockIdx.z];
+    if (blockIdx.x >= (uint32_t)J.NB || blockIdx.y >= J.sets) return;
+    const int T = blockDim.x, t = threadIdx.x;
+    const uint32_t set = blockIdx.y;
+    const size_t base = (size_t)(set / J.G) * Bp + J.bucket_off + (size_t)(set % J.G) * J.nb;
+    XYZZ<F> acc = XYZZ<F>::inf(), tot = XYZZ<F>::inf();
+    if (t < J.T) {
+        const XYZZ<F> *E = buckets + base + ((size_t)blockIdx.x * J.T + t) * J.L;
+        for (int u = J.L - 1; u >= 0; u--) {
+            acc.add(ld_vec(E + u));
+            tot.add(acc);
+        }
+    }
+    XYZZ<F> incl = acc;
+    block_suffix_scan(sm, T, t, incl);
+    XYZZ<F> above = XYZZ<F>::inf();
+    if (t + 1 < T) above = sm_get<XYZZ<F>>(sm, T, t + 1);
+    __syncthreads();
+    for (int i = 0; i < J.logL; i++) above = above.dbl();
+    tot.add(above);
+    block_sum(sm, T, t, tot);
+    if (t == 0) {
+        XYZZ<F> *o = out + 2 * ((size_t)J.l1_off + (size_t)set * J.NB + blockIdx.x);
+        st_vec(o, tot);
+        st_vec(o + 1, incl);
+    }
+}
+template <class F>
+__global__ void __launch_bounds__(128)
+k_reduce_l2_jobs(const XYZZ<F> *__restrict__ l1, RedGeoTab tab, XYZZ<F> *__restrict__ out)
+{
+    extern __shared__ uint32_t sm[];
+    const RedGeo &J = tab.g[blockIdx.y];
+    if (blockIdx.x >= J.sets) return;
+    const int T = blockDim.x, t = threadIdx.x;
+    const uint32_t set = blockIdx.x;
+    XYZZ<F> R = XYZZ<F>::inf(), S = XYZZ<F>::inf();
+    if (t < J.NB) {
+        R = ld_vec(l1 + 2 * ((size_t)J.l1_off + (size_t)set * J.NB + t));
+        S = ld_vec(l1 + 2 * ((size_t)J.l1_off + (size_t)set * J.NB + t) + 1);
+    }
+    block_suffix_scan(sm, T, t, S);
+    XYZZ<F> v = (t >= 1 && t < J.NB) ? S : XYZZ<F>::inf();
+    block_sum(sm, T, t, v);
+    __syncthreads();
+    block_sum(sm, T, t, R);
+    if (t == 0) {
+        for (int i = 0; i < J.logCH; i++) v = v.dbl();
+        R.add(v);
+        st_vec(out + J.l2_off + set, R);
+    }
+}
+template <class F>
+__global__ void k_final_jobs(const XYZZ<F> *__restrict__ sets, int batch, RedGeoTab tab, int njobs, XYZZ<F> *__restrict__ res)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x, job = blockIdx.y;
+    if (p >= batch) return;
+    const RedGeo &J = tab.g[job];
+    const XYZZ<F> *s = sets + J.l2_off + (size_t)p * J.G;
+    XYZZ<F> r = ld_vec(s + (J.G - 1));
+    for (int g = (int)J.G - 2; g >= 0; g--) {
+        for (int i = 0; i < J.c; i++) r = r.dbl();
+        r.add(ld_vec(s + g));
+    }
+    st_vec(res + (size_t)p * njobs + job, r);
+}
+
 // ---- the same weighted sum for large bucket sets, without a scan over the buckets -------------------------------
 // View the nb = H2 * W2 buckets of a set as a grid, b = hi * W2 + lo:
 //     sum_b (b + 1) E_b  =  W2 * sum_hi hi * Row_hi  +  sum_lo (lo + 1) * Col_lo,   Row_hi = sum_lo E, Col_lo = sum_hi E.
@@ -450,6 +535,53 @@ int msm_finish(zkb_ctx *ctx, const MsmPlan *plan, const JobTab &tab, int batch, 
         ZKB_LAUNCH_CHECK(ctx);
         k_fixup_wide_sum<F><<<(unsigned)ctx->sm_count * 8, 128, 128 * sizeof(PT), st>>>(buckets, wide, max_chunks, chunk_sums);
         ZKB_LAUNCH_CHECK(ctx);
+    }
+    // several jobs, none with enough buckets for the row / column form: one launch per level for all of them
+    bool together = tab.njobs > 1;
+    for (uint32_t q = 0; q < tab.njobs && together; q++) {
+        const uint32_t nb = 1u << (tab.j[q].c - 1);
+        const size_t sets = (size_t)batch * tab.j[q].G;
+        if (sets > 65535 || (nb >= 1024 && nb <= 65536 && sets * nb >= (size_t)ctx->sm_count * 2048)) together = false;
+    }
+    if (together) {
+        RedGeoTab gt = {};
+        size_t l1_total = 0, l2_total = 0, max_sets = 0;
+        int max_nb_blocks = 0;
+        for (uint32_t q = 0; q < tab.njobs; q++) {
+            const MsmJob &J = tab.j[q];
+            RedGeo &g = gt.g[q];
+            g.bucket_off = J.bucket_off;
+            g.G = J.G;
+            g.c = J.c;
+            g.nb = 1u << (J.c - 1);
+            g.sets = (uint32_t)((size_t)batch * J.G);
+            g.T = (int)(g.nb < 128 ? g.nb : 128);
+            const size_t all_buckets = (size_t)g.nb * J.G * batch;
+            int L = 1;
+            while (L < 8 && L < (int)(g.nb / g.T) && all_buckets / (2 * L) >= (size_t)ctx->sm_count * 512) L <<= 1;
+            while (g.nb / ((uint32_t)g.T * L) > 128) L <<= 1;
+            g.L = L;
+            g.NB = (int)(g.nb / ((uint32_t)g.T * L));
+            if (g.NB > 128) return fail(ctx, ZKB_ERR_ARG, "msm: window too wide for the bucket reduction");
+            while ((1 << g.logL) < L) g.logL++;
+            while ((1u << g.logCH) < (uint32_t)g.T * L) g.logCH++;
+            g.l1_off = (uint32_t)l1_total;
+            g.l2_off = (uint32_t)l2_total;
+            l1_total += (size_t)g.sets * g.NB;
+            l2_total += g.sets;
+            max_sets = std::max(max_sets, (size_t)g.sets);
+            max_nb_blocks = std::max(max_nb_blocks, g.NB);
+        }
+        ZKB_CUDA(ctx, ctx->scratch[gs + SB_L1].ensure(2 * l1_total * sizeof(PT)));
+        ZKB_CUDA(ctx, ctx->scratch[gs + SB_L2].ensure(l2_total * sizeof(PT)));
+        PT *l1 = ctx->scratch[gs + SB_L1].as<PT>(), *l2 = ctx->scratch[gs + SB_L2].as<PT>();
+        k_reduce_l1_jobs<F><<<dim3((unsigned)max_nb_blocks, (unsigned)max_sets, tab.njobs), 128, 128 * sizeof(PT), st>>>(buckets, tab.Bp, gt, l1);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_reduce_l2_jobs<F><<<dim3((unsigned)max_sets, tab.njobs), 128, 128 * sizeof(PT), st>>>(l1, gt, l2);
+        ZKB_LAUNCH_CHECK(ctx);
+        k_final_jobs<F><<<dim3(ceil_div((size_t)batch, 32), tab.njobs), 32, 0, st>>>(l2, batch, gt, (int)tab.njobs, d_res);
+        ZKB_LAUNCH_CHECK(ctx);
+        return ZKB_OK;
     }
     for (uint32_t q = 0; q < tab.njobs; q++) {
         const MsmJob &J = tab.j[q];

@@ -32,7 +32,6 @@ namespace {
 
 constexpr int NTT_T = 256;     // threads per block
 constexpr int NTT_EMAX = 2048; // elements staged per block (64 KB of shared memory)
-constexpr int NTT_TILE_DEFAULT = 11;
 #ifndef NTT_TFAST
 #define NTT_TFAST 1 // 1: lanes walk the t index in the staging loops (coalesced rows, but shared-memory stride C); 0: always the column index
 #endif
@@ -405,11 +404,16 @@ int r2_levels(zkb_ctx *ctx, const R2Tables &T, bool inverse, bool dit, Fr *a, si
         ZKB_CUDA(ctx, cudaFuncSetAttribute(k_ntt_r8<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         ctx->func_attr_done |= 1u;
     }
-    static const int tile_log = [] { // development knob: ZKB_NTT_TILE = 10 or 11
+    static const int tile_env = [] { // development knob: ZKB_NTT_TILE = 10 or 11
         const char *e = getenv("ZKB_NTT_TILE");
         const int v = e ? atoi(e) : 0;
-        return v == 10 || v == 11 ? v : NTT_TILE_DEFAULT;
+        return v == 10 || v == 11 ? v : 0;
     }();
+    // 1 024-element tiles (128 threads, four blocks per SM: the load / compute / store phases of neighbouring blocks
+    // interleave better) unless 2 048-element tiles save a whole pass (a pass takes at most tile_log - 2 levels).
+    // Measured (witness map, ms, tile 10 / 11): 2^16 0.287 / 0.309, 2^17 0.416 / 0.441, 2^18 0.609 / 0.584 (3 passes
+    // against 2), 2^19 1.03 / 1.10, 2^20 1.97 / 2.08, 2^21 3.87 / 3.98, 2^22 7.85 / 8.03.
+    const int tile_log = tile_env ? tile_env : (L >= 18 && (L + 8) / 9 < (L + 7) / 8) ? 11 : 10;
     NttPlan pl;
     ntt_plan_transform(&pl, L, dit, tile_log);
     if (fuse)
