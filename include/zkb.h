@@ -363,7 +363,9 @@ typedef struct zkb_vk_desc {
 /* r1cs_gg_ppzksnark_verifier_strong_IC (r1cs_gg_ppzksnark.tcc:523-622, reached from libsnark_verify,
  * zklaim/libsnark_wrapper.cpp:252-276) for n proofs under one key.  primary: n x num_inputs Fr (Montgomery);
  * proofs: n x 48 limbs in the layout zkb_prove writes (A 12, B 24, C 12: Jacobian).  accept[i] = 1 when the
- * reference verifier returns true for proof i, else 0 (a point off its curve, or the pairing equation failing). */
+ * reference verifier returns true for proof i, else 0 (a point off its curve, or the pairing equation failing).  A proof
+ * coordinate >= q or an input >= r is not a canonical residue: such a proof is rejected (accept[i] = 0).  n x max(num_inputs, 1)
+ * must stay below 2^29 per call (the input-sum kernels index their lanes with 32 bits): larger batches are refused. */
 int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primary, const uint64_t *proofs, size_t n,
                      int32_t *accept);
 

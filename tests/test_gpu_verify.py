@@ -48,6 +48,28 @@ def test_verify_batch_matches_golden_decisions(zctx):
     assert zctx.verify_batch(vk, g["primary"][:0], g["proofs"][:0]).tolist() == []
 
 
+def test_non_canonical_encodings_are_rejected(zctx):
+    """A coordinate >= q or a public input >= r is not something the reference could have serialised (Fp_model keeps
+    residues canonical, fp.tcc): adding the modulus to a limb group of a VALID proof must turn accept into reject, for
+    the proof concerned only."""
+    g = np.load(os.path.join(GOLD, "verify.npz"))
+    vk = {k: g[k] for k in ("alpha_g1_beta_g2", "gamma_g2", "delta_g2", "gamma_ABC_g1")}
+    Q = 21888242871839275222246405745257275088696311157297823662689037894645226208583
+    R = 21888242871839275222246405745257275088548364400416034343698204186575808495617
+
+    def plus(limbs, m):
+        v = int.from_bytes(np.ascontiguousarray(limbs, dtype="<u8").tobytes(), "little") + m
+        assert v < 1 << 256
+        return np.frombuffer(v.to_bytes(32, "little"), dtype="<u8")
+
+    proofs, primary = g["proofs"][:4].copy(), g["primary"][:4].copy()
+    assert zctx.verify_batch(vk, primary, proofs).tolist() == [True] * 4
+    proofs[1, 0:4] = plus(proofs[1, 0:4], Q)            # A.X + q
+    proofs[2, 44:48] = plus(proofs[2, 44:48], Q)        # C.Z + q
+    primary[3, 0] = plus(primary[3, 0], R)              # first public input + r
+    assert zctx.verify_batch(vk, primary, proofs).tolist() == [True, False, False, False]
+
+
 def test_zklaim_batch_prove_then_verify_on_gpu(zctx, ref):
     """64 credential proofs made by zkb_prove_batch, verified by zkb_verify_batch; every decision equals the
     reference verifier's (valid proofs, a swapped C, a wrong public input)."""

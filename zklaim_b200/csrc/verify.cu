@@ -326,6 +326,9 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
         return fail(ctx, ZKB_ERR_ARG, "zkb_verify_batch: bad argument");
     if (n == 0) return ZKB_OK;
     if (n > (1u << 24) || vk->num_inputs > (1u << 24)) return fail(ctx, ZKB_ERR_ARG, "zkb_verify_batch: batch too large");
+    // the input-sum kernels index their lanes with 32 bits
+    if ((uint64_t)n * (vk->num_inputs ? vk->num_inputs : 1) * VF_CHUNKS >= ((uint64_t)1 << 32) || 3 * (uint64_t)n >= ((uint64_t)1 << 31))
+        return fail(ctx, ZKB_ERR_ARG, "zkb_verify_batch: proofs x inputs exceeds 2^32 / 8 lanes: verify in smaller batches");
     ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
     const PairingConsts *K;
     int rc = consts_on_device(ctx, &K);
@@ -361,6 +364,7 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
         // window table of the key: rebuilt only when gamma_ABC_g1 changes
         const size_t abc_words = (size_t)(ni + 1) * 8;
         const bool same = ctx->vf_abc_host.size() == abc_words && !memcmp(ctx->vf_abc_host.data(), vk->gamma_ABC_g1, abc_words * 8);
+        if (!same) ctx->vf_abc_host.clear(); // before the buffer may move: a failed call must not leave a stale "same key" behind
         ZKB_CUDA(ctx, ctx->scratch[SV_TAB].ensure((size_t)ni * VF_CHUNKS * sizeof(G1Affine)));
         G1Affine *d_tab = ctx->scratch[SV_TAB].as<G1Affine>();
         if (!same) {
@@ -401,6 +405,23 @@ int zkb_verify_batch(zkb_ctx *ctx, const zkb_vk_desc *vk, const uint64_t *primar
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_ms = ms;
     memcpy(accept, ctx->pinned, n * sizeof(int32_t));
+    // untrusted input: the field arithmetic assumes canonical residues (< q for coordinates, < r for inputs).  An encoding
+    // outside that range is not a proof the reference could have serialised: rejected here, whatever the kernels made of it.
+    {
+        static const uint64_t Q[4] = {0x3c208c16d87cfd47ull, 0x97816a916871ca8dull, 0xb85045b68181585dull, 0x30644e72e131a029ull};
+        static const uint64_t R[4] = {0x43e1f593f0000001ull, 0x2833e84879b97091ull, 0xb85045b68181585dull, 0x30644e72e131a029ull};
+        auto below = [](const uint64_t *x, const uint64_t *m) {
+            for (int i = 3; i >= 0; i--)
+                if (x[i] != m[i]) return x[i] < m[i];
+            return false;
+        };
+        for (size_t i = 0; i < n; i++) {
+            bool ok = true;
+            for (int k = 0; k < 12 && ok; k++) ok = below(proofs + i * 48 + 4 * k, Q);
+            for (size_t k = 0; k < vk->num_inputs && ok; k++) ok = below(primary + (i * vk->num_inputs + k) * 4, R);
+            if (!ok) accept[i] = 0;
+        }
+    }
     return ZKB_OK;
 }
 
