@@ -9,8 +9,13 @@ namespace zkb {
 // ------------------------------------------------------------------------------------
 // The sorted list holds point entries only; which bucket a position belongs to follows from start[]: a thread finds
 // the bucket of its first position by binary search and then walks the boundaries.
+// resident blocks per SM asked of the compiler for G1 (106 registers, no spills at 4).  Measured: 5 blocks (102
+// registers, 84 B of spill loads) 6.19 ms against 6.21 ms per batch-64 launch -- noise; 6 blocks (85 registers) 6.37 ms.
+#ifndef ZKB_ACC_MIN_BLOCKS_G1
+#define ZKB_ACC_MIN_BLOCKS_G1 4
+#endif
 template <class F>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, sizeof(F) == 32 ? ZKB_ACC_MIN_BLOCKS_G1 : 1)
 k_accumulate(const Affine<F> *__restrict__ pts, const uint32_t *__restrict__ ent, const uint32_t *__restrict__ start,
              uint32_t B, uint32_t rmax, XYZZ<F> *__restrict__ buckets, XYZZ<F> *__restrict__ parts)
 {
