@@ -71,7 +71,12 @@ enum { ZKB_NTT_FFT = 0, ZKB_NTT_IFFT = 1, ZKB_NTT_COSET_FFT = 2, ZKB_NTT_ICOSET_
 
 /* ---- lifetime ---------------------------------------------------------------------- */
 /* Creates a context on CUDA device `device_id`.  Fails (ZKB_ERR_CUDA) when no GPU is
- * present: there is no CPU fallback anywhere in this library. */
+ * present: there is no CPU fallback anywhere in this library.
+ * A context = its own CUDA streams and scratch memory, used by one host thread at a time.  SEVERAL contexts may live
+ * on one device: a key or base set (zkb_key_upload, zkb_bases_upload) is immutable once uploaded and tuned and may be
+ * used by every context of its device at once.  That is how a proving service keeps a GPU full: a few caller threads,
+ * one context each, one batch in flight each -- the latency-bound tail of one batch (fix-ups, bucket reduction,
+ * assembly) runs under the throughput-bound kernels of another (bench.py: 12.3 -> 11.4 ms per batch of 64 with four). */
 int zkb_init(int device_id, zkb_ctx **out);
 void zkb_shutdown(zkb_ctx *ctx);
 const char *zkb_last_error(const zkb_ctx *ctx); /* ctx may be NULL: last error of zkb_init */
@@ -211,7 +216,10 @@ typedef struct {
  * does not satisfy the system: the device checks <a,z> * <b,z> == <c,z> for every constraint
  * (r1cs_constraint_system::is_satisfied, which the reference asserts, :406-408, and which
  * zklaim's generate_proof tests on the host, snark.cpp:119-124); the proof of such a witness
- * is returned as all-zero limbs. */
+ * is returned as all-zero limbs.
+ * Host buffers may be pageable or pinned.  A pageable assignment of 16 MB or more (the 124 MB of a 2^22-constraint
+ * circuit, a whole batch) is copied into a pinned area of the context by several host threads, 2 MB pieces each followed by
+ * its own asynchronous transfer (ZKB_STAGED_UPLOAD=0: plain cudaMemcpy). */
 int zkb_prove(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4],
               zkb_proof *out, uint64_t *H_out);
 
@@ -238,7 +246,8 @@ int zkb_prove_combine(zkb_ctx *ctx, const zkb_partial *parts, size_t n, const ui
  * alike: SpMV, iFFT, coset FFT -- three independent chains).  Three shards run one chain each, one shard divides and
  * transforms back, every shard receives the H coefficients; the exchanges (two m x 32-byte vectors in, one out) are
  * the caller's -- NCCL send / recv / broadcast in zklaim_b200/sharding.py, peer copies in a single process:
- *   _begin   uploads w, r, s, starts the shard's witness-only sums (A, B-in-G1, B-in-G2 ranges) on side streams and, for
+ *   _begin   uploads w, r, s (w: host memory, or device memory of this context's GPU -- e.g. a witness gathered over
+ *            NVLink from one range per rank), starts the shard's witness-only sums (A, B-in-G1, B-in-G2 ranges) on side streams and, for
  *            which = 0 / 1 / 2, writes the coset evaluations of polynomial A / B / C to d_part (device, m x 4 limbs);
  *            which = -1: no chain.  check != 0: this shard also evaluates all three products and tests
  *            <a,z><b,z> = <c,z> per constraint (its _end then reports ZKB_ERR_UNSAT); one shard should do so.

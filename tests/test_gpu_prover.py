@@ -71,6 +71,43 @@ def test_zklaim_batch_of_distinct_witnesses(zctx, ref, zklaim1):
         assert circ.verify(ws[i][: d["num_inputs"]], got[i])
 
 
+def test_contexts_of_one_device_share_a_key(zctx, ref, zklaim1):
+    """include/zkb.h, zkb_init: several contexts on one device, one host thread each, all proving under ONE uploaded key
+    at the same time (bench.py's proof streams).  Every stream's proofs must equal the reference prover's for the same
+    (w, r, s), whatever the other streams are doing."""
+    import threading
+    circ, key = zklaim1
+    d = circ.dims()
+    streams, rounds, n = 3, 3, 4
+    ctxs = [zk.Context(0) for _ in range(streams)]
+    ws = [np.stack([ref.zklaim_witness(1, 900 + 10 * j + i, d["num_variables"]) for i in range(n)]) for j in range(streams)]
+    rs = [ref.sha512_rng(9100 + j, n) for j in range(streams)]
+    ss = [ref.sha512_rng(9200 + j, n) for j in range(streams)]
+    out = [[None] * rounds for _ in range(streams)]
+    err = []
+
+    def body(j):
+        try:
+            for k in range(rounds):
+                out[j][k] = ctxs[j].prove_batch(key, ws[j], rs[j], ss[j])
+        except Exception as e:
+            err.append(e)
+
+    th = [threading.Thread(target=body, args=(j,)) for j in range(streams)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not err, err
+    for j in range(streams):
+        want = [_norm_proof(ref, circ.prove(ws[j][i], rs[j][i], ss[j][i], want_H=False)["proof"]) for i in range(n)]
+        for k in range(rounds):
+            for i in range(n):
+                assert np.array_equal(_norm_proof(ref, out[j][k][i]), want[i]), (j, k, i)
+    for c in ctxs:
+        c.close()
+
+
 def test_pipelined_batches_equal_plain_batches(zctx, ref, zklaim1):
     """zkb_prove_batch_submit / _collect (inputs of batch k + 1 travel while batch k computes, two staging slots):
     same proofs as zkb_prove_batch, in submission order; an unsatisfying batch is reported by ITS collect only; a
