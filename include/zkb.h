@@ -257,6 +257,9 @@ int zkb_prove_combine(zkb_ctx *ctx, const zkb_partial *parts, size_t n, const ui
  * One proof in flight per context.  zkb_last_device_ms() after _end = the device time of the three calls. */
 int zkb_prove_split_begin(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, const uint64_t r[4], const uint64_t s[4], int which,
                           int check, void *d_part);
+/* one more chain on a shard that has run _begin (two GPUs: shard 0 takes A and C, shard 1 takes B): the coset evaluations
+ * of polynomial `which` to d_part. */
+int zkb_prove_split_chain(zkb_ctx *ctx, const zkb_key *key, int which, void *d_part);
 int zkb_prove_split_combine(zkb_ctx *ctx, const zkb_key *key, void *d_abc, void *d_H_plain);
 int zkb_prove_split_end(zkb_ctx *ctx, const zkb_key *key, const void *d_H_plain, zkb_partial *out);
 

@@ -351,7 +351,7 @@ def test_witness_map_at_scale_bit_exact(zctx, ref, nc, kind):
     circ.free()
 
 
-@pytest.mark.parametrize("world", [3, 5])
+@pytest.mark.parametrize("world", [2, 3, 5])
 def test_one_proof_with_the_witness_map_split_by_polynomial(zctx, ref, world):
     """SURVEY 8(e) optional row: ranks 0 / 1 / 2 compute the coset evaluations of A / B / C (zkb_prove_split_begin), one
     rank divides and transforms back (zkb_prove_split_combine), every rank finishes its share from the H coefficients
@@ -377,6 +377,8 @@ def test_one_proof_with_the_witness_map_split_by_polynomial(zctx, ref, world):
             for k in range(world):
                 ctxs[k].prove_split_begin(keys[k], witness, r, s, k if k < 3 else -1, check=(k == world - 1),
                                           d_part=abc[k].data_ptr() if k < 3 else 0)
+            if world == 2:  # rank 0 takes A and C (zkb_prove_split_chain)
+                ctxs[0].prove_split_chain(keys[0], 2, abc[2].data_ptr())
             ctxs[0].prove_split_combine(keys[0], abc.data_ptr(), H.data_ptr())
             parts, failed = [], 0
             for k in range(world):

@@ -132,6 +132,9 @@ class FakeDevice:                        # records the data flow of zkb_prove_sp
         self.checked = check
         assert (which >= 0) == (d_part != 0)
         if which >= 0: view(d_part, M * 4)[:] = 1000 * (which + 1) + np.arange(M * 4, dtype=np.uint64)
+    def prove_split_chain(self, key, which, d_part):
+        assert self.rank == 0 and which == 2  # two ranks: rank 0 also takes C
+        view(d_part, M * 4)[:] = 1000 * (which + 1) + np.arange(M * 4, dtype=np.uint64)
     def prove_split_combine(self, key, d_abc, d_H):
         abc = view(d_abc, 3 * M * 4).reshape(3, M * 4)
         for k in range(3): assert abc[k][0] == 1000 * (k + 1) and abc[k][5] == 1000 * (k + 1) + 5, abc[k][:8]
@@ -158,10 +161,10 @@ sys.exit(0 if ok else 1)
 """
 
 
-@pytest.mark.parametrize("world", [3, 4])
+@pytest.mark.parametrize("world", [2, 3, 4])
 def test_split_witness_map_orchestration_gloo(tmp_path, world):
     """sharding.sharded_prove_split over gloo with a device that records the data flow: ranks 0 / 1 / 2 produce the three
-    coset vectors, rank 0 receives the other two in order and combines, every rank receives the same H and contributes its
+    coset vectors (two ranks: rank 0 produces A and C), rank 0 receives the others in order and combines, every rank receives the same H and contributes its
     share in rank order; only the last rank is asked to check satisfiability."""
     script = tmp_path / "split_worker.py"
     script.write_text(SPLIT_WORKER.format(root=ROOT, port=_free_port(), world=world))

@@ -81,6 +81,7 @@ SYMBOLS = {
     "zkb_prove_partial": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _u64p, _u64p]),
     "zkb_prove_combine": (_i, [_vp, _u64p, _sz, _u64p, _u64p, _vp]),
     "zkb_prove_split_begin": (_i, [_vp, _vp, _u64p, _u64p, _u64p, _i, _i, _vp]),
+    "zkb_prove_split_chain": (_i, [_vp, _vp, _i, _vp]),
     "zkb_prove_split_combine": (_i, [_vp, _vp, _vp, _vp]),
     "zkb_prove_split_end": (_i, [_vp, _vp, _vp, _u64p]),
     "zkb_key_tune": (_i, [_vp, _vp, _u64p]),
@@ -415,6 +416,10 @@ class Context:
             wp = C.c_void_p(w.ctypes.data)
         self._chk(self.lib.zkb_prove_split_begin(self.h, key.h, wp, r.ctypes.data, s.ctypes.data, which, 1 if check else 0,
                                                  C.c_void_p(d_part)))
+
+    def prove_split_chain(self, key: "Key", which: int, d_part: int) -> None:
+        """zkb_prove_split_chain: one more polynomial (0 / 1 / 2) to the coset on a context that has run prove_split_begin"""
+        self._chk(self.lib.zkb_prove_split_chain(self.h, key.h, which, C.c_void_p(d_part)))
 
     def prove_split_combine(self, key: "Key", d_abc: int, d_H: int) -> None:
         self._chk(self.lib.zkb_prove_split_combine(self.h, key.h, C.c_void_p(d_abc), C.c_void_p(d_H)))

@@ -1130,6 +1130,37 @@ int zkb_prove_split_begin(zkb_ctx *ctx, const zkb_key *key, const uint64_t *w, c
     return ZKB_OK;
 }
 
+int zkb_prove_split_chain(zkb_ctx *ctx, const zkb_key *key, int which, void *d_part)
+{
+    if (!ctx || !key || which < 0 || which > 2 || !d_part) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_chain: bad argument");
+    if (key->dev != ctx->dev) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_chain: key lives on another device");
+    ZKB_CUDA(ctx, cudaSetDevice(ctx->dev));
+    cudaStream_t st = ctx->stream;
+    const size_t m = key->m;
+    if (ctx->scratch[SP_Z].cap < key->zlen * sizeof(Fr)) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_chain: call zkb_prove_split_begin first");
+    ZKB_CUDA(ctx, ctx->scratch[SP_ABC].ensure((size_t)3 * m * sizeof(Fr)));
+    Fr *abc = ctx->scratch[SP_ABC].as<Fr>();
+    Fr *tmp = nullptr;
+    if (key->kind != ZKB_DOMAIN_BASIC_RADIX2) {
+        ZKB_CUDA(ctx, ctx->scratch[SP_TMP].ensure((size_t)3 * m * sizeof(Fr)));
+        tmp = ctx->scratch[SP_TMP].as<Fr>();
+    }
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev2, st));
+    int rc = spmv_stage(ctx, key, 1, abc, which, 1);
+    if (!rc) rc = domain_to_coset(ctx, &key->dom, abc + (size_t)which * m, m, 1, tmp);
+    if (rc) {
+        cudaDeviceSynchronize();
+        return rc;
+    }
+    ZKB_CUDA(ctx, cudaMemcpyAsync(d_part, abc + (size_t)which * m, m * sizeof(Fr), cudaMemcpyDeviceToDevice, st));
+    ZKB_CUDA(ctx, cudaEventRecord(ctx->ev3, st));
+    ZKB_CUDA(ctx, cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3);
+    ctx->last_ms += ms;
+    return ZKB_OK;
+}
+
 int zkb_prove_split_combine(zkb_ctx *ctx, const zkb_key *key, void *d_abc, void *d_H_plain)
 {
     if (!ctx || !key || !d_abc || !d_H_plain) return fail(ctx, ZKB_ERR_ARG, "zkb_prove_split_combine: bad argument");

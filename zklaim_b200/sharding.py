@@ -83,9 +83,10 @@ def sharded_prove(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndarray, g
 
 def sharded_prove_split(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndarray, group=None, device: Optional[str] = None,
                         trace: Optional[dict] = None) -> np.ndarray:
-    """ONE Groth16 proof over all ranks with the witness map SPLIT by polynomial instead of replicated (needs >= 3 ranks;
-    fewer fall back to sharded_prove).  r1cs_to_qap_witness_map treats A, B and C alike (r1cs_to_qap.tcc:240-293): ranks
-    0 / 1 / 2 run SpMV + iFFT + coset FFT of one polynomial each (zkb_prove_split_begin), ranks 1 and 2 send their m x 32
+    """ONE Groth16 proof over all ranks with the witness map SPLIT by polynomial instead of replicated (needs >= 2 ranks;
+    one rank falls back to sharded_prove).  r1cs_to_qap_witness_map treats A, B and C alike (r1cs_to_qap.tcc:240-293): ranks
+    0 / 1 / 2 run SpMV + iFFT + coset FFT of one polynomial each (zkb_prove_split_begin; with two ranks, rank 0 takes A and
+    C -- zkb_prove_split_chain -- and rank 1 takes B), ranks 1 and 2 send their m x 32
     bytes to rank 0 (NCCL send / recv), rank 0 divides by Z and transforms back (zkb_prove_split_combine), broadcasts the H
     coefficients, and every rank computes its share of the H + L sum (zkb_prove_split_end); the witness-only sums run on
     side streams from the start.  The last rank also checks satisfiability.  Exchanges: 2 x 32 m bytes in, 32 m bytes out.
@@ -97,7 +98,7 @@ def sharded_prove_split(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndar
     import torch
     import torch.distributed as dist
 
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 3:
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 2:
         return sharded_prove(ctx, key_shard, w, r, s, group, device)
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     dev = torch.device(device if device is not None else ("cuda" if dist.get_backend(group) == "nccl" else "cpu"))
@@ -108,6 +109,7 @@ def sharded_prove_split(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndar
 
     m = key_shard.domain()[0]
     which = rank if rank < 3 else -1
+    senders = [1, 2] if world >= 3 else [1]  # ranks whose polynomial travels to rank 0
     abc = torch.empty((3, m, 4), dtype=torch.int64, device=dev) if rank == 0 else None
     part = abc[0] if rank == 0 else (torch.empty((m, 4), dtype=torch.int64, device=dev) if which >= 0 else None)
     H = torch.empty((m, 4), dtype=torch.int64, device=dev)
@@ -134,15 +136,17 @@ def sharded_prove_split(ctx, key_shard, w: np.ndarray, r: np.ndarray, s: np.ndar
     sync()
     mark("witness: one range per rank over PCIe, all_gather over NVLink")
     ctx.prove_split_begin(key_shard, w_arg, r, s, which, check=(rank == world - 1), d_part=part.data_ptr() if part is not None else 0)
+    if rank == 0 and world == 2:
+        ctx.prove_split_chain(key_shard, 2, abc[2].data_ptr())
     mark("begin: own polynomial to the coset (ranks 0-2)")
     if rank == 0:
-        for q in dist.batch_isend_irecv([dist.P2POp(dist.irecv, abc[1], 1, group), dist.P2POp(dist.irecv, abc[2], 2, group)]):
+        for q in dist.batch_isend_irecv([dist.P2POp(dist.irecv, abc[k], k, group) for k in senders]):
             q.wait()
         sync()
         mark("recv 2 x 32 m bytes")
         ctx.prove_split_combine(key_shard, abc.data_ptr(), H.data_ptr())
         mark("combine: (A B - C) / Z, coset back to coefficients")
-    elif rank in (1, 2):
+    elif rank in senders:
         for q in dist.batch_isend_irecv([dist.P2POp(dist.isend, part, 0, group)]):
             q.wait()
     dist.broadcast(H, src=0, group=group)
