@@ -400,7 +400,7 @@ def extra_sharded(ctx, np, torch, dist, zk, bridge, rank, world, local, imad_pea
                             "equals_replicated_form": bool(np.array_equal(norm(proof_r), norm(proof_s))),
                             "key_shard_device_gb": key.device_bytes() / 1e9,
                             "phases_ms_wall_rank0": {k: round(v, 3) for k, v in phases.items()},
-                            "form": "witness map split by polynomial over ranks 0-2 (world >= 3; else replicated), H broadcast; "
+                            "form": "witness map split by polynomial over ranks 0-2 (two ranks: rank 0 takes A and C), H broadcast; "
                                     "ms_device = max over ranks of the library's CUDA-event time (NCCL exchanges are in ms_wall only)"}
     key.free()
     return out
