@@ -20,7 +20,7 @@ for line in out.splitlines():
         continue
     if hist is None:
         continue
-    m = re.match(r"\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
+    m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
     if m:
         hist[m.group(1)] += 1
 if hist is not None:
