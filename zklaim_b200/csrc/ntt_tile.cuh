@@ -112,7 +112,9 @@ ZKB_HD size_t ntt_gidx(const NttPass &P, uint32_t blk, int t, int col)
 // ---- load / store phases: lanes walk consecutive global addresses ------------------------------------------
 // (Measured and rejected in round 2: letting the first round load and the last round store straight from / to global
 //  memory, without the staging here -- the lanes of a round then touch 32 different 128-byte lines per instruction:
-//  witness map at 2^22 8.13 -> 8.38 ms.)
+//  witness map at 2^22 8.13 -> 8.38 ms.  Also rejected: dropping the UNIT round variant to shrink the kernel from
+//  8 560 to 6 496 SASS instructions (137 -> 104 KB; the profile shows instruction-fetch stalls): the seven extra
+//  products by w^0 per thread cost more than the fetches, 7.83 -> 8.05 ms.)
 // Optional fused steps of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:270-311), used by its last transform only:
 struct NttFuse {
     const Fr *B, *C; // load: the staged value becomes (a * B[i] - C[i]) * zinv   (H on the coset, divided by Z)
