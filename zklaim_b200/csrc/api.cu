@@ -75,7 +75,10 @@ int upload_rows(zkb_ctx *ctx, void *dst, size_t dpitch, const void *src, size_t 
     nt = nt < 1 ? 1 : nt > 8 ? 8 : nt;
     if ((size_t)nt > npieces) nt = (unsigned)npieces;
     std::vector<std::thread> helpers;
-    for (unsigned t = 1; t < nt; t++) helpers.emplace_back(work);
+    try {
+        for (unsigned t = 1; t < nt; t++) helpers.emplace_back(work);
+    } catch (const std::exception &) { // no more threads to be had: the ones that started and this one share the pieces
+    }
     work();
     for (auto &h : helpers) h.join();
     if (bad.load()) {
