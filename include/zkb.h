@@ -292,8 +292,9 @@ int zkb_prove_batch_collect(zkb_ctx *ctx, zkb_proof *out);
  * A pool owns one zkb_ctx per device and drives them with one host thread per device; a C caller shaped like
  * zklaim/main_benchmark.c:174-198 (credential after credential through the prover) uses every GPU of the box
  * through these calls without Python or NCCL.  zkb_pool_init(NULL, 0, ..) takes all visible devices.
- *   zkb_pool_prove_batch     independent proofs: the batch is cut into one contiguous slice per device (key replicated
- *                            by zkb_pool_key_upload); results in submission order;
+ *   zkb_pool_prove_batch     independent proofs: the batch is cut into one contiguous slice per context (key replicated
+ *                            per DEVICE by zkb_pool_key_upload: a device id listed twice gives two contexts that share
+ *                            one replica); results in submission order;
  *   zkb_pool_msm             one MSM, bases range-sharded the way libff::multi_exp chunks them (multiexp.tcc:417-431):
  *                            device i holds and sums chunk i, the 96- / 192-byte partials are added on device 0
  *                            (multiexp.tcc:433-438);

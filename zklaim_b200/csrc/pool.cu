@@ -22,6 +22,7 @@ struct zkb_key_set {
     zkb_pool *pool = nullptr;
     bool sharded = false;
     std::vector<zkb_key *> keys;
+    std::vector<char> owns; // contexts of one device share ONE replica (a device key is immutable): the first one owns it
 };
 struct zkb_bases_set {
     zkb_pool *pool = nullptr;
@@ -128,15 +129,30 @@ static int key_set_build(zkb_pool *p, const zkb_key_desc *desc, bool sharded, zk
     ks->pool = p;
     ks->sharded = sharded;
     ks->keys.assign(p->ctx.size(), nullptr);
+    ks->owns.assign(p->ctx.size(), 1);
     const int world = (int)p->ctx.size();
+    std::vector<int> first(p->ctx.size()); // the first context on the same device
+    for (size_t i = 0; i < p->ctx.size(); i++) {
+        first[i] = (int)i;
+        for (size_t j = 0; j < i && !sharded; j++)
+            if (p->ctx[j]->dev == p->ctx[i]->dev) {
+                first[i] = (int)j;
+                ks->owns[i] = 0;
+                break;
+            }
+    }
     const int rc = on_all(p, [&](int i) {
+        if (!ks->owns[i]) return (int)ZKB_OK;
         return sharded ? zkb_key_upload_shard(p->ctx[i], desc, i, world, &ks->keys[i]) : zkb_key_upload(p->ctx[i], desc, &ks->keys[i]);
     });
     if (rc) {
-        for (zkb_key *k : ks->keys) zkb_key_free(k);
+        for (size_t i = 0; i < ks->keys.size(); i++)
+            if (ks->owns[i]) zkb_key_free(ks->keys[i]);
         delete ks;
         return rc;
     }
+    for (size_t i = 0; i < ks->keys.size(); i++)
+        if (!ks->owns[i]) ks->keys[i] = ks->keys[first[i]];
     *out = ks;
     return ZKB_OK;
 }
@@ -147,7 +163,7 @@ int zkb_pool_key_upload_sharded(zkb_pool *p, const zkb_key_desc *desc, zkb_key_s
 int zkb_pool_key_tune(zkb_pool *p, zkb_key_set *ks, const uint64_t *w)
 {
     if (!p || !ks || !w || ks->pool != p) return pool_fail(p, ZKB_ERR_ARG, "zkb_pool_key_tune: bad argument");
-    return on_all(p, [&](int i) { return zkb_key_tune(p->ctx[i], ks->keys[i], w); });
+    return on_all(p, [&](int i) { return ks->owns[i] ? zkb_key_tune(p->ctx[i], ks->keys[i], w) : (int)ZKB_OK; });
 }
 
 const zkb_key *zkb_pool_key(const zkb_key_set *ks, int i) { return ks && i >= 0 && (size_t)i < ks->keys.size() ? ks->keys[i] : nullptr; }
@@ -155,7 +171,8 @@ const zkb_key *zkb_pool_key(const zkb_key_set *ks, int i) { return ks && i >= 0 
 void zkb_pool_key_free(zkb_key_set *ks)
 {
     if (!ks) return;
-    for (zkb_key *k : ks->keys) zkb_key_free(k);
+    for (size_t i = 0; i < ks->keys.size(); i++)
+        if (ks->owns[i]) zkb_key_free(ks->keys[i]);
     delete ks;
 }
 
