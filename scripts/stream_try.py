@@ -1,3 +1,5 @@
+"""How many caller threads / batches per caller does the zklaim-facing stream (zkb_libsnark_prove_batch, bridge) need?
+Development aid behind bench.py's e2e_zklaim (3 callers x 10 batches).  Usage: python scripts/stream_try.py"""
 import os, sys, json
 sys.path.insert(0, os.getcwd())
 from zklaim_b200 import bridge
